@@ -1,0 +1,25 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+@pytest.fixture(scope="session")
+def filters():
+    from whisper_tflite_b200 import synth
+    return synth.mel_filters()
+
+
+@pytest.fixture(scope="session")
+def oracle_built():
+    from oracle import mel as omel
+    omel.build()
+    return omel
