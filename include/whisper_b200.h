@@ -1,0 +1,127 @@
+/* whisper_b200.h — C ABI of the B200-native Whisper inference path.
+ *
+ * This is the drop-in boundary: the host-side C++ mirror of the reference's whisper.h
+ * (whisper_tflite_b200/csrc/host/whisper.h: Engine / EncDec / Monolith / create_engine /
+ * log_mel_spectrogram) calls ONLY these entry points, in the places where the reference calls
+ * into tflite::Interpreter. Plain pointers and sizes; no C++ or torch types; every function
+ * returns a wt_status, never throws, never exits. One engine per device; calls on one engine
+ * must be serialised by the caller (same contract as the reference, whose Java layer holds a lock
+ * around the engine: io/github/jerinphilip/whisper/Whisper.java:109-113).
+ *
+ * Reference interface each entry replaces (paths relative to /root/reference):
+ *   wt_engine_create / _destroy   Atom::Atom — FlatBufferModel::BuildFromFile + InterpreterBuilder +
+ *                                 AllocateTensors (whisper.tflite/whisper.cpp:261-271); Encoder/Decoder
+ *                                 ctors (:284, :311-312); `delete engine` in JNI destroy
+ *                                 (bindings/java/whisper.tflite.cpp:36-42)
+ *   wt_set_mel_filters            Filters filled by Reader::read_filters (whisper.cpp:519-545) and passed to
+ *                                 log_mel_spectrogram (whisper.h:121-123)
+ *   wt_log_mel                    whisper::log_mel_spectrogram (whisper.cpp:109-216)
+ *   wt_encode                     Encoder::forward: memcpy mel -> typed_input_tensor<float>(0), Invoke,
+ *                                 output_tensor(0) (whisper.cpp:285-309)
+ *   wt_decode_greedy              Decoder::forward: encoder states -> input 0, prompt, ResizeInputTensor /
+ *                                 AllocateTensors / Invoke / argmax loop (whisper.cpp:314-403)
+ *   wt_transcribe_tokens          Monolith::transcribe's mel -> Invoke -> typed_output_tensor<int>(0)
+ *                                 (whisper.cpp:692-732) and EncDec::transcribe's mel -> encoder -> decoder
+ *                                 (whisper.cpp:752-765), batched
+ */
+#ifndef WHISPER_B200_H_
+#define WHISPER_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WT_API __attribute__((visibility("default")))
+
+typedef struct wt_engine wt_engine;
+
+typedef enum wt_status {
+  WT_OK = 0,
+  WT_ERR_INVALID = 1, /* bad argument */
+  WT_ERR_CUDA = 2,    /* CUDA runtime/driver error (no device, launch failure, OOM) */
+  WT_ERR_IO = 3,      /* weight file missing/unreadable */
+  WT_ERR_FORMAT = 4,  /* weight file malformed / unsupported dims */
+  WT_ERR_STATE = 5    /* call order (e.g. decode before encode, filters not set) */
+} wt_status;
+
+typedef enum wt_precision {
+  WT_PRECISION_BF16 = 0,       /* bf16 operands, f32 accumulate: tcgen05/TMEM GEMMs (production) */
+  WT_PRECISION_FP32_VERIFY = 1 /* f32 operands and accumulators end to end: token-identity checks */
+} wt_precision;
+
+typedef enum wt_mem { WT_HOST = 0, WT_DEVICE = 1 } wt_mem;
+
+typedef struct wt_config {
+  int32_t struct_size; /* = sizeof(wt_config) */
+  int32_t precision;   /* wt_precision */
+  int32_t max_batch;   /* clips per call the engine is sized for (>= 1) */
+  int32_t keep_logits; /* != 0: keep the f32 logits of every decode step (debug/parity; costs B*27*V*4 bytes) */
+} wt_config;
+
+typedef struct wt_dims {
+  int32_t n_mels, n_audio_ctx, d_model, n_heads, n_enc_layers, n_dec_layers, n_vocab, n_text_ctx;
+} wt_dims;
+
+#define WT_N_SAMPLES 480000 /* kSampleRate * kChunkSize, whisper.h:34,38 */
+#define WT_N_FRAMES 3000    /* kMelLen, whisper.h:39 */
+#define WT_N_MEL 80         /* kNMEL, whisper.h:36 */
+#define WT_N_FREQ 201       /* 1 + kNFFT/2, whisper.cpp:129 */
+#define WT_MAX_TOKENS 31    /* 4 prompt + 27 generated, whisper.cpp:364-367 */
+
+/* Loads `weights_path` (<prefix>.b200w, see whisper_tflite_b200/synth.py) onto `device`, builds the execution
+ * plan and returns a handle. weights_path == NULL creates a frontend-only engine (wt_log_mel works,
+ * encode/decode return WT_ERR_STATE). */
+WT_API int wt_engine_create(const wt_config* cfg, const char* weights_path, int device, wt_engine** out);
+WT_API void wt_engine_destroy(wt_engine* e);
+WT_API int wt_engine_dims(const wt_engine* e, wt_dims* out);
+
+/* filters: [n_mel=80][n_freq=201] f32 row-major, host memory (Filters.data, whisper.h:96-101). */
+WT_API int wt_set_mel_filters(wt_engine* e, const float* filters, int n_mel, int n_freq);
+
+/* Work is enqueued on `cuda_stream` (a cudaStream_t; NULL = the engine's own stream). Calls taking only
+ * WT_DEVICE buffers return after enqueueing; calls touching a WT_HOST buffer synchronise before returning. */
+WT_API int wt_set_stream(wt_engine* e, void* cuda_stream);
+WT_API int wt_synchronize(wt_engine* e);
+
+/* pcm [n_clips][n_samples] f32 -> mel_out [n_clips][80][n_samples/160] f32 (reference layout j*n_len+i).
+ * n_samples <= 480000 per clip. mel_out may be NULL (result stays resident for wt_encode(mel=NULL)). */
+WT_API int wt_log_mel(wt_engine* e, const float* pcm, int n_clips, int n_samples, int pcm_mem, float* mel_out,
+                      int out_mem);
+
+/* mel [n_clips][80][3000] f32 (NULL = use the engine-resident mel of the last wt_log_mel) ->
+ * states_out [n_clips][1500][d_model] f32 (may be NULL). Encoder states and the cross-attention K/V stay
+ * resident for wt_decode_greedy. */
+WT_API int wt_encode(wt_engine* e, const float* mel, int n_clips, int mel_mem, float* states_out, int out_mem);
+
+/* Greedy loop of Decoder::forward over the resident encoder states. prompt: host int64[prompt_len].
+ * ids_out [n_clips][max_total_tokens] int32 (prompt included, -1 padded), lens_out [n_clips] int32. */
+WT_API int wt_decode_greedy(wt_engine* e, int n_clips, const int64_t* prompt, int prompt_len, int max_total_tokens,
+                            int64_t eot, int32_t* ids_out, int32_t* lens_out, int out_mem);
+
+/* pcm -> token ids in one call (mel + encoder + decoder; nothing but ids/lens leaves the device). */
+WT_API int wt_transcribe_tokens(wt_engine* e, const float* pcm, int n_clips, int n_samples, int pcm_mem,
+                                const int64_t* prompt, int prompt_len, int max_total_tokens, int64_t eot,
+                                int32_t* ids_out, int32_t* lens_out, int out_mem);
+
+/* keep_logits engines only: f32 logits of decode step `step` (0 = first generated token), [n_clips][n_vocab]. */
+WT_API int wt_get_step_logits(wt_engine* e, int step, int n_clips, float* out, int out_mem);
+
+/* Number of kernel launches this engine has enqueued since creation (bench.py's gpu_launches). */
+WT_API int64_t wt_launch_count(const wt_engine* e);
+
+/* Thread-local description of the last failure on this thread. */
+WT_API const char* wt_last_error(void);
+WT_API const char* wt_version(void);
+
+/* Stand-alone tcgen05 GEMM entry used by the kernel-level parity tests and the micro-benchmark:
+ * C[M][N] (bf16) = epi(A[M][K] . W[N][K]^T), all device pointers, bf16 row-major, f32 bias.
+ * flags: 1 bias, 2 GELU. */
+WT_API int wt_debug_gemm_bf16(void* cuda_stream, const void* A, const void* W, const float* bias, void* C, int M, int N,
+                              int K, int flags);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WHISPER_B200_H_ */

@@ -1,0 +1,199 @@
+"""ctypes binding of include/whisper_b200.h — the call a Python user makes.
+
+Host arrays are numpy; device arrays are anything exposing ``data_ptr()`` (torch CUDA tensors).
+There is no CPU implementation behind these calls: if the CUDA library is missing or no B200 is
+visible, construction raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import synth
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "csrc", "libwhisper_b200.so")
+
+WT_HOST, WT_DEVICE = 0, 1
+PRECISION_BF16, PRECISION_FP32_VERIFY = 0, 1
+REFERENCE_PROMPT = (50258, 50261, 50359, 50363)  # whisper.cpp:331 (multilingual, "de")
+EOT_MULTILINGUAL = 50257
+MAX_TOKENS = 31
+
+EXPORTED = [
+    "wt_engine_create", "wt_engine_destroy", "wt_engine_dims", "wt_set_mel_filters", "wt_set_stream",
+    "wt_synchronize", "wt_log_mel", "wt_encode", "wt_decode_greedy", "wt_transcribe_tokens",
+    "wt_get_step_logits", "wt_launch_count", "wt_last_error", "wt_version", "wt_debug_gemm_bf16",
+]
+
+
+class WtConfig(ctypes.Structure):
+    _fields_ = [("struct_size", ctypes.c_int32), ("precision", ctypes.c_int32), ("max_batch", ctypes.c_int32),
+                ("keep_logits", ctypes.c_int32)]
+
+
+class WtDims(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in ("n_mels", "n_audio_ctx", "d_model", "n_heads", "n_enc_layers",
+                                              "n_dec_layers", "n_vocab", "n_text_ctx")]
+
+
+class WhisperB200Error(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise WhisperB200Error(
+                f"{LIB_PATH} is missing: build it with `python -m whisper_tflite_b200.build` "
+                "(the CUDA library is the product; there is no CPU fallback)")
+        lib = ctypes.CDLL(LIB_PATH)
+        lib.wt_last_error.restype = ctypes.c_char_p
+        lib.wt_version.restype = ctypes.c_char_p
+        lib.wt_launch_count.restype = ctypes.c_int64
+        lib.wt_launch_count.argtypes = [ctypes.c_void_p]
+        lib.wt_engine_destroy.restype = None
+        lib.wt_engine_destroy.argtypes = [ctypes.c_void_p]
+        _lib = lib
+    return _lib
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise WhisperB200Error(f"wt_status {rc}: {load_library().wt_last_error().decode()}")
+
+
+def _ptr_mem(a):
+    """-> (address, WT_HOST|WT_DEVICE, keepalive)"""
+    if a is None:
+        return None, WT_DEVICE, None
+    if isinstance(a, np.ndarray):
+        assert a.flags["C_CONTIGUOUS"]
+        return a.ctypes.data, WT_HOST, a
+    if hasattr(a, "data_ptr"):  # torch tensor
+        assert a.is_contiguous()
+        return a.data_ptr(), (WT_DEVICE if a.is_cuda else WT_HOST), a
+    raise TypeError(type(a))
+
+
+class Engine:
+    """One engine per device; not re-entrant (same contract as the reference's Engine)."""
+
+    def __init__(self, weights_path: Optional[str], device: int = 0, max_batch: int = 1,
+                 precision: int = PRECISION_BF16, keep_logits: bool = False, filters: Optional[np.ndarray] = None):
+        self.lib = load_library()
+        cfg = WtConfig(ctypes.sizeof(WtConfig), precision, max_batch, int(keep_logits))
+        h = ctypes.c_void_p()
+        _check(self.lib.wt_engine_create(ctypes.byref(cfg), weights_path.encode() if weights_path else None,
+                                         int(device), ctypes.byref(h)))
+        self.h = h
+        self.max_batch = max_batch
+        self.precision = precision
+        self.device = device
+        self.dims = None
+        if weights_path:
+            d = WtDims()
+            _check(self.lib.wt_engine_dims(self.h, ctypes.byref(d)))
+            self.dims = d
+        self.set_mel_filters(synth.mel_filters() if filters is None else filters)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.wt_engine_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_mel_filters(self, filters: np.ndarray):
+        f = np.ascontiguousarray(filters, dtype=np.float32)
+        _check(self.lib.wt_set_mel_filters(self.h, ctypes.c_void_p(f.ctypes.data), f.shape[0], f.shape[1]))
+
+    def set_stream(self, cuda_stream: int):
+        _check(self.lib.wt_set_stream(self.h, ctypes.c_void_p(cuda_stream)))
+
+    def synchronize(self):
+        _check(self.lib.wt_synchronize(self.h))
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.wt_launch_count(self.h))
+
+    # ---- whisper::log_mel_spectrogram, batched ----
+    def log_mel(self, pcm, out=None):
+        p, mem, _k = _ptr_mem(pcm)
+        n_clips, n_samples = pcm.shape
+        if out is None:
+            out = np.empty((n_clips, 80, n_samples // 160), dtype=np.float32)
+        o, omem, _k2 = _ptr_mem(out)
+        _check(self.lib.wt_log_mel(self.h, ctypes.c_void_p(p), n_clips, n_samples, mem, ctypes.c_void_p(o), omem))
+        return out
+
+    # ---- Encoder::forward ----
+    def encode(self, mel=None, n_clips: Optional[int] = None, out=None, want_states: bool = True):
+        p, mem, _k = _ptr_mem(mel)
+        if mel is not None:
+            n_clips = mel.shape[0]
+        if out is None and want_states:
+            out = np.empty((n_clips, self.dims.n_audio_ctx, self.dims.d_model), dtype=np.float32)
+        o, omem, _k2 = _ptr_mem(out)
+        _check(self.lib.wt_encode(self.h, ctypes.c_void_p(p) if p else None, n_clips, mem,
+                                  ctypes.c_void_p(o) if o else None, omem))
+        return out
+
+    # ---- Decoder::forward ----
+    def decode_greedy(self, n_clips: int, prompt: Sequence[int] = REFERENCE_PROMPT, max_total_tokens: int = MAX_TOKENS,
+                      eot: int = EOT_MULTILINGUAL, ids_out=None, lens_out=None):
+        pr = (ctypes.c_int64 * len(prompt))(*[int(t) for t in prompt])
+        if ids_out is None:
+            ids_out = np.empty((n_clips, max_total_tokens), dtype=np.int32)
+            lens_out = np.empty((n_clips,), dtype=np.int32)
+        i, imem, _k = _ptr_mem(ids_out)
+        l, lmem, _k2 = _ptr_mem(lens_out)
+        assert imem == lmem
+        _check(self.lib.wt_decode_greedy(self.h, n_clips, pr, len(prompt), max_total_tokens, ctypes.c_int64(eot),
+                                         ctypes.c_void_p(i), ctypes.c_void_p(l), imem))
+        return ids_out, lens_out
+
+    # ---- Monolith / EncDec transcribe minus detokenisation, batched ----
+    def transcribe_tokens(self, pcm, prompt: Sequence[int] = REFERENCE_PROMPT, max_total_tokens: int = MAX_TOKENS,
+                          eot: int = EOT_MULTILINGUAL, ids_out=None, lens_out=None):
+        p, mem, _k = _ptr_mem(pcm)
+        n_clips, n_samples = pcm.shape
+        pr = (ctypes.c_int64 * len(prompt))(*[int(t) for t in prompt])
+        if ids_out is None:
+            ids_out = np.empty((n_clips, max_total_tokens), dtype=np.int32)
+            lens_out = np.empty((n_clips,), dtype=np.int32)
+        i, imem, _k2 = _ptr_mem(ids_out)
+        l, lmem, _k3 = _ptr_mem(lens_out)
+        assert imem == lmem
+        _check(self.lib.wt_transcribe_tokens(self.h, ctypes.c_void_p(p), n_clips, n_samples, mem, pr, len(prompt),
+                                             max_total_tokens, ctypes.c_int64(eot), ctypes.c_void_p(i),
+                                             ctypes.c_void_p(l), imem))
+        return ids_out, lens_out
+
+    def step_logits(self, step: int, n_clips: int) -> np.ndarray:
+        out = np.empty((n_clips, self.dims.n_vocab), dtype=np.float32)
+        _check(self.lib.wt_get_step_logits(self.h, step, n_clips, ctypes.c_void_p(out.ctypes.data), WT_HOST))
+        return out
+
+
+def debug_gemm_bf16(a, w, bias, c, flags: int = 0, stream: int = 0):
+    """C[M][N] = epi(A[M][K] . W[N][K]^T) on torch CUDA bf16 tensors through the tcgen05 kernel."""
+    lib = load_library()
+    M, K = a.shape
+    N = w.shape[0]
+    _check(lib.wt_debug_gemm_bf16(ctypes.c_void_p(stream), ctypes.c_void_p(a.data_ptr()), ctypes.c_void_p(w.data_ptr()),
+                                  ctypes.c_void_p(bias.data_ptr()) if bias is not None else None,
+                                  ctypes.c_void_p(c.data_ptr()), M, N, K, flags | (1 if bias is not None else 0)))
+    return c

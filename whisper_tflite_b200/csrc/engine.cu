@@ -1,0 +1,1022 @@
+// Engine behind the C ABI in include/whisper_b200.h: device-resident weights + execution plan for the
+// Whisper hot path (log-mel -> encoder -> KV-cached greedy decoder) on one B200.
+//
+// It takes the place of the reference's `Atom` (FlatBufferModel + InterpreterBuilder + Interpreter,
+// whisper.cpp:261-271) and of the three Interpreter::Invoke call sites (whisper.cpp:295, :375, :719).
+// There is no CPU fallback: every entry point fails with WT_ERR_CUDA when no sm_100 device is usable.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <climits>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include "../../include/whisper_b200.h"
+#include "gemm_sm100.cuh"
+#include "mel_host.h"
+#include "mel_kernels.cuh"
+#include "simt_kernels.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+#define WT_CUDA_OK(expr)                                                                              \
+  do {                                                                                                \
+    cudaError_t _e = (expr);                                                                          \
+    if (_e != cudaSuccess) return fail(WT_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                                       __FILE__, __LINE__);                                           \
+  } while (0)
+#define WT_TRY(expr)             \
+  do {                           \
+    int _s = (expr);             \
+    if (_s != WT_OK) return _s;  \
+  } while (0)
+
+using bf16 = __nv_bfloat16;
+using wt::RowMap;
+
+uint16_t f32_to_bf16_bits(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return 0x7fc0;
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+
+// ------------------------------------------------------------------------------------------------
+// weight file (<prefix>.b200w, written by whisper_tflite_b200/synth.py::write_weight_file)
+// ------------------------------------------------------------------------------------------------
+struct HostTensor {
+  const float* data;
+  std::vector<int64_t> shape;
+  size_t numel() const {
+    size_t n = 1;
+    for (auto d : shape) n *= (size_t)d;
+    return n;
+  }
+};
+struct WeightFile {
+  void* base = nullptr;
+  size_t size = 0;
+  wt_dims dims{};
+  std::map<std::string, HostTensor> t;
+  ~WeightFile() {
+    if (base) munmap(base, size);
+  }
+  int open(const char* path) {
+    int fd = ::open(path, O_RDONLY);
+    if (fd < 0) return fail(WT_ERR_IO, "cannot open weight file %s", path);
+    struct stat st;
+    if (fstat(fd, &st) != 0) {
+      ::close(fd);
+      return fail(WT_ERR_IO, "cannot stat %s", path);
+    }
+    size = (size_t)st.st_size;
+    base = mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0);
+    ::close(fd);
+    if (base == MAP_FAILED) {
+      base = nullptr;
+      return fail(WT_ERR_IO, "cannot mmap %s", path);
+    }
+    const uint8_t* p = (const uint8_t*)base;
+    if (size < 48 || memcmp(p, "WTB200W\x01", 8) != 0) return fail(WT_ERR_FORMAT, "%s: bad magic", path);
+    uint32_t version, n;
+    memcpy(&version, p + 8, 4);
+    memcpy(&n, p + 12, 4);
+    if (version != 1) return fail(WT_ERR_FORMAT, "%s: unsupported version %u", path, version);
+    int32_t d[8];
+    memcpy(d, p + 16, 32);
+    dims = {d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7]};
+    size_t off = 48;
+    for (uint32_t i = 0; i < n; ++i) {
+      if (off + 2 > size) return fail(WT_ERR_FORMAT, "%s: truncated index", path);
+      uint16_t ln;
+      memcpy(&ln, p + off, 2);
+      off += 2;
+      if (off + ln + 2 > size) return fail(WT_ERR_FORMAT, "%s: truncated index", path);
+      std::string name((const char*)p + off, ln);
+      off += ln;
+      uint8_t dt = p[off], nd = p[off + 1];
+      off += 2;
+      if (dt != 0 || nd > 4) return fail(WT_ERR_FORMAT, "%s: tensor %s has unsupported dtype/rank", path, name.c_str());
+      HostTensor ht;
+      ht.shape.resize(nd);
+      if (off + 8 * nd + 16 > size) return fail(WT_ERR_FORMAT, "%s: truncated index", path);
+      memcpy(ht.shape.data(), p + off, 8 * nd);
+      off += 8 * nd;
+      uint64_t o, nb;
+      memcpy(&o, p + off, 8);
+      memcpy(&nb, p + off + 8, 8);
+      off += 16;
+      if (o + nb > size || nb != ht.numel() * 4) return fail(WT_ERR_FORMAT, "%s: tensor %s out of bounds", path, name.c_str());
+      ht.data = (const float*)(p + o);
+      t[name] = ht;
+    }
+    return WT_OK;
+  }
+  const HostTensor* find(const std::string& name, std::initializer_list<int64_t> shape) const {
+    auto it = t.find(name);
+    if (it == t.end()) {
+      fail(WT_ERR_FORMAT, "weight file lacks tensor %s", name.c_str());
+      return nullptr;
+    }
+    if (it->second.shape != std::vector<int64_t>(shape)) {
+      fail(WT_ERR_FORMAT, "tensor %s has the wrong shape", name.c_str());
+      return nullptr;
+    }
+    return &it->second;
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda link dependency)
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// bf16 tensor, 128B swizzle, inner box 64 elements. dims/strides innermost first; strides in bytes for dims 1..rank-1.
+int make_map_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                  const uint32_t* box) {
+  EncodeTiledFn fn = get_encode_tiled();
+  if (!fn) return fail(WT_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  cuuint64_t gd[5];
+  cuuint64_t gs[5];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) {
+    gd[i] = dims[i];
+    bx[i] = box[i];
+    es[i] = 1;
+    if (i > 0) gs[i - 1] = strides_bytes[i - 1];
+  }
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(WT_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) rank=%d dims=[%llu,%llu,%llu] stride0=%llu", (int)r,
+                rank, (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0),
+                (unsigned long long)(rank > 2 ? dims[2] : 0), (unsigned long long)(rank > 1 ? strides_bytes[0] : 0));
+  return WT_OK;
+}
+
+struct Lin {            // y = x . W^T + b
+  void* w = nullptr;    // [N][K] f32 or bf16 depending on precision
+  float* b = nullptr;   // [N] f32 (may be null)
+  int N = 0, K = 0;
+};
+struct LNp { float* g = nullptr; float* b = nullptr; };
+struct EncLayer { LNp ln1, ln2; Lin qkv, out, fc1, fc2; };
+struct DecLayer { LNp ln1, lnx, ln2; Lin qkv, out, xq, xkv, xout, fc1, fc2; void *kx = nullptr, *vx = nullptr, *kc = nullptr, *vc = nullptr; };
+
+}  // namespace
+
+// ================================================================================================
+struct wt_engine {
+  int device = 0;
+  int precision = WT_PRECISION_BF16;
+  int max_batch = 1;
+  int keep_logits = 0;
+  bool has_model = false;
+  wt_dims dims{};
+  int num_sms = 148;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  int64_t launches = 0;
+  std::vector<void*> allocs;
+
+  // mel frontend
+  bool filters_set = false;
+  int n_mel = 80;
+  float *d_hann = nullptr, *d_tw400 = nullptr, *d_fw = nullptr;
+  int *d_frow = nullptr, *d_flen = nullptr;
+  float *d_pcm = nullptr, *d_mel_raw = nullptr, *d_mel = nullptr;
+  int* d_clip_max = nullptr;
+  int mel_clips = 0, mel_len = 0;  // what d_mel_raw currently holds
+
+  // model
+  size_t esz = 2;  // activation/weight element size
+  Lin conv1, conv2;
+  void* enc_pos = nullptr;      // [1500][d] T
+  float* enc_pos_f32 = nullptr; // verify mode addend
+  std::vector<EncLayer> enc;
+  LNp ln_post, dec_ln;
+  void *tok_emb = nullptr, *dec_pos = nullptr;  // T
+  std::vector<DecLayer> dec;
+  // activations
+  void *mel_tm = nullptr, *x1 = nullptr, *x = nullptr, *xn = nullptr, *att = nullptr, *qkv = nullptr, *hbuf = nullptr,
+       *enc_out = nullptr;
+  void *dx = nullptr, *dxn = nullptr, *datt = nullptr, *dqkv = nullptr, *dq = nullptr, *dh = nullptr;
+  float *logits = nullptr, *step_logits = nullptr, *io_f32 = nullptr, *xa_part = nullptr;
+  unsigned* xa_tickets = nullptr;
+  unsigned long long* argmax_part = nullptr;
+  int *tokens = nullptr, *lens = nullptr, *done = nullptr, *d_prompt = nullptr;
+  int enc_clips = 0;  // clips whose encoder states / cross K,V are resident
+  std::map<std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint64_t, uint64_t, uint32_t>, CUtensorMap> map_cache;
+
+  ~wt_engine() {
+    cudaSetDevice(device);
+    if (own_stream) cudaStreamSynchronize(own_stream);
+    for (void* p : allocs) cudaFree(p);
+    if (own_stream) cudaStreamDestroy(own_stream);
+  }
+
+  template <class T>
+  int alloc(T** out, size_t count, bool zero = false) {
+    void* p = nullptr;
+    size_t bytes = count * sizeof(T);
+    if (bytes == 0) bytes = 16;
+    WT_CUDA_OK(cudaMalloc(&p, bytes));
+    allocs.push_back(p);
+    if (zero) WT_CUDA_OK(cudaMemset(p, 0, bytes));
+    *out = (T*)p;
+    return WT_OK;
+  }
+  int alloc_bytes(void** out, size_t bytes, bool zero = false) {
+    uint8_t* p;
+    WT_TRY(alloc<uint8_t>(&p, bytes, zero));
+    *out = p;
+    return WT_OK;
+  }
+  int upload_f32(float** out, const float* host, size_t n) {
+    WT_TRY(alloc<float>(out, n));
+    WT_CUDA_OK(cudaMemcpy(*out, host, n * 4, cudaMemcpyHostToDevice));
+    return WT_OK;
+  }
+  // uploads in the engine's operand precision
+  int upload_T(void** out, const float* host, size_t n) {
+    if (precision == WT_PRECISION_FP32_VERIFY) {
+      float* p;
+      WT_TRY(upload_f32(&p, host, n));
+      *out = p;
+      return WT_OK;
+    }
+    std::vector<uint16_t> tmp(n);
+    for (size_t i = 0; i < n; ++i) tmp[i] = f32_to_bf16_bits(host[i]);
+    uint16_t* p;
+    WT_TRY(alloc<uint16_t>(&p, n));
+    WT_CUDA_OK(cudaMemcpy(p, tmp.data(), n * 2, cudaMemcpyHostToDevice));
+    *out = p;
+    return WT_OK;
+  }
+  int check_launch(const char* what) {
+    ++launches;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(WT_ERR_CUDA, "launch of %s failed: %s", what, cudaGetErrorString(e));
+    return WT_OK;
+  }
+  bool f32mode() const { return precision == WT_PRECISION_FP32_VERIFY; }
+
+  int init_frontend();
+  int load_model(const char* path);
+  int set_filters(const float* f, int n_mel_, int n_freq);
+  int log_mel(const float* pcm, int n_clips, int n_samples, int pcm_mem, float* out, int out_mem, bool finalize);
+  int encode(const float* mel, int n_clips, int mel_mem, float* states_out, int out_mem, bool from_raw);
+  int decode(int n_clips, const int64_t* prompt, int prompt_len, int max_total, int64_t eot, int32_t* ids, int32_t* lens_o,
+             int out_mem);
+
+  // ---- op wrappers ----
+  int gemm_bf16(const void* A, const uint64_t* a_dims, const uint64_t* a_strides, int rows_per_batch, int n_batches,
+                const Lin& L, int K_total, int taps, int tap_k, const int* tap_c0, const int* tap_row, void* C,
+                RowMap cmap, int flags, const void* addend, RowMap add_map, unsigned long long* amax, int force_bn = 0);
+  int linear(const void* A, int M, const Lin& L, void* C, int flags, const void* addend = nullptr,
+             unsigned long long* amax = nullptr);
+  int layernorm(const void* in, const LNp& ln, void* out, int rows);
+  int get_map(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides,
+              const uint32_t* box);
+};
+
+int wt_engine::get_map(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides,
+                       const uint32_t* box) {
+  auto key = std::make_tuple(base, dims[0], rank > 1 ? dims[1] : 0, rank > 2 ? dims[2] : 0, rank > 1 ? strides[0] : 0,
+                             rank > 2 ? strides[1] : 0, (uint32_t)(box[1] * 4 + rank));
+  auto it = map_cache.find(key);
+  if (it != map_cache.end()) {
+    *out = it->second;
+    return WT_OK;
+  }
+  WT_TRY(make_map_bf16(out, base, rank, dims, strides, box));
+  map_cache[key] = *out;
+  return WT_OK;
+}
+
+template <int BN>
+static int launch_gemm_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMap& mw, wt::GemmBf16Params& p) {
+  using S = wt::GemmSmem<BN>;
+  static bool attr_set[64] = {};
+  if (!attr_set[e->device & 63]) {
+    WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+    attr_set[e->device & 63] = true;
+  }
+  p.n_tiles_n = (p.N + BN - 1) / BN;
+  const int n_tiles = p.tiles_per_batch * p.n_batches * p.n_tiles_n;
+  const int grid = n_tiles < e->num_sms ? n_tiles : e->num_sms;
+  wt::gemm_bf16_sm100_kernel<BN><<<grid, wt::kGemmThreads, S::kTotal, e->stream>>>(ma, mw, p);
+  return e->check_launch("gemm_bf16_sm100_kernel");
+}
+
+static int pick_bn(int M, int N) {
+  if (M <= 128) return N >= 16384 ? 128 : 64;
+  const int cands[3] = {256, 192, 128};
+  for (int bn : cands)
+    if (N % bn == 0) return bn;
+  return 128;
+}
+
+int wt_engine::gemm_bf16(const void* A, const uint64_t* a_dims, const uint64_t* a_strides, int rows_per_batch,
+                         int n_batches, const Lin& L, int K_total, int taps, int tap_k, const int* tap_c0,
+                         const int* tap_row, void* C, RowMap cmap, int flags, const void* addend, RowMap add_map,
+                         unsigned long long* amax, int force_bn) {
+  const int M = rows_per_batch * n_batches;
+  const int bn = force_bn ? force_bn : pick_bn(M, L.N);
+  CUtensorMap ma, mw;
+  const uint32_t abox[3] = {64, 128, 1};
+  WT_TRY(get_map(&ma, A, 3, a_dims, a_strides, abox));
+  const uint64_t wdims[2] = {(uint64_t)K_total, (uint64_t)L.N};
+  const uint64_t wstr[1] = {(uint64_t)K_total * 2};
+  const uint32_t wbox[2] = {64, (uint32_t)bn};
+  WT_TRY(get_map(&mw, L.w, 2, wdims, wstr, wbox));
+  wt::GemmBf16Params p{};
+  p.bias = L.b;
+  p.addend = (const bf16*)addend;
+  p.add_map = add_map;
+  p.C = C;
+  p.cmap = cmap;
+  p.argmax_part = amax;
+  p.M = M;
+  p.N = L.N;
+  p.K = K_total;
+  p.rows_per_batch = rows_per_batch;
+  p.tiles_per_batch = (rows_per_batch + 127) / 128;
+  p.n_batches = n_batches;
+  p.flags = flags | (L.b ? wt::EPI_BIAS : 0);
+  if (!L.b) p.flags &= ~wt::EPI_BIAS;
+  p.taps = taps;
+  p.tap_k = tap_k;
+  const int per_tap_k = taps == 1 ? K_total : tap_k;
+  p.kblocks_per_tap = (per_tap_k + 63) / 64;
+  for (int i = 0; i < 3; ++i) {
+    p.tap_c0[i] = (i < taps && tap_c0) ? tap_c0[i] : 0;
+    p.tap_row[i] = (i < taps && tap_row) ? tap_row[i] : 0;
+  }
+  switch (bn) {
+    case 64: return launch_gemm_bn<64>(this, ma, mw, p);
+    case 128: return launch_gemm_bn<128>(this, ma, mw, p);
+    case 192: return launch_gemm_bn<192>(this, ma, mw, p);
+    case 256: return launch_gemm_bn<256>(this, ma, mw, p);
+  }
+  return fail(WT_ERR_INVALID, "bad BN %d", bn);
+}
+
+// y[M][N] = epi(x[M][K] . W^T) on plain row-major operands, either precision. addend = residual [M][N] (may alias C).
+int wt_engine::linear(const void* A, int M, const Lin& L, void* C, int flags, const void* addend,
+                      unsigned long long* amax) {
+  RowMap plain{0, M, L.N};
+  if (f32mode()) {
+    wt::GemmF32Params p{};
+    p.A = (const float*)A;
+    p.amap = RowMap{0, M, L.K};
+    p.W = (const float*)L.w;
+    p.bias = L.b;
+    p.residual = (const float*)addend;
+    p.rmap = plain;
+    p.pos = nullptr;
+    p.pos_rows = 1;
+    p.C = (float*)C;
+    p.cmap = plain;
+    p.M = M;
+    p.N = L.N;
+    p.K = L.K;
+    p.flags = (flags & (wt::EPI_GELU)) | (L.b ? wt::EPI_BIAS : 0) | (addend ? wt::EPI_RESIDUAL : 0);
+    dim3 grid((L.N + 63) / 64, (M + 63) / 64);
+    wt::sgemm_f32_kernel<<<grid, 256, 0, stream>>>(p);
+    return check_launch("sgemm_f32_kernel");
+  }
+  const uint64_t ad[3] = {(uint64_t)L.K, (uint64_t)M, 1};
+  const uint64_t as[2] = {(uint64_t)L.K * 2, (uint64_t)L.K * 2 * (uint64_t)M};
+  return gemm_bf16(A, ad, as, M, 1, L, L.K, 1, 0, nullptr, nullptr, C, plain, flags | (addend ? wt::EPI_ADD : 0), addend,
+                   plain, amax);
+}
+
+int wt_engine::layernorm(const void* in, const LNp& ln, void* out, int rows) {
+  const int D = dims.d_model;
+  dim3 grid((rows + 7) / 8);
+  if (f32mode())
+    wt::layernorm_kernel<float, float><<<grid, 256, 0, stream>>>((const float*)in, ln.g, ln.b, (float*)out, rows, D);
+  else
+    wt::layernorm_kernel<bf16, bf16><<<grid, 256, 0, stream>>>((const bf16*)in, ln.g, ln.b, (bf16*)out, rows, D);
+  return check_launch("layernorm_kernel");
+}
+
+int wt_engine::init_frontend() {
+  const size_t B = (size_t)max_batch;
+  WT_TRY(alloc(&d_pcm, B * WT_N_SAMPLES));
+  WT_TRY(alloc(&d_mel_raw, B * wt::kMaxMel * WT_N_FRAMES));
+  WT_TRY(alloc(&d_mel, B * wt::kMaxMel * WT_N_FRAMES));
+  WT_TRY(alloc(&d_clip_max, B));
+  WT_CUDA_OK(cudaFuncSetAttribute(wt::mel_frames_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::kMelSmemBytes));
+  return WT_OK;
+}
+
+int wt_engine::set_filters(const float* f, int n_mel_, int n_freq) {
+  if (!f || n_freq != WT_N_FREQ || n_mel_ < 1 || n_mel_ > wt::kMaxMel)
+    return fail(WT_ERR_INVALID, "filters must be [n_mel<=%d][201]", wt::kMaxMel);
+  if (has_model && n_mel_ != dims.n_mels) return fail(WT_ERR_INVALID, "model expects %d mel bins", dims.n_mels);
+  wt::MelHostTables t = wt::build_mel_tables(f, n_mel_, n_freq);
+  n_mel = n_mel_;
+  WT_TRY(upload_f32(&d_hann, t.hann.data(), t.hann.size()));
+  WT_TRY(upload_f32(&d_tw400, t.tw400.data(), t.tw400.size()));
+  if (t.fw.empty()) t.fw.push_back(0.0f);
+  WT_TRY(upload_f32(&d_fw, t.fw.data(), t.fw.size()));
+  WT_TRY(alloc(&d_frow, t.frow.size()));
+  WT_CUDA_OK(cudaMemcpy(d_frow, t.frow.data(), t.frow.size() * 4, cudaMemcpyHostToDevice));
+  WT_TRY(alloc(&d_flen, t.flen.size()));
+  WT_CUDA_OK(cudaMemcpy(d_flen, t.flen.data(), t.flen.size() * 4, cudaMemcpyHostToDevice));
+  filters_set = true;
+  return WT_OK;
+}
+
+// pcm -> raw log10 mel + per-clip max (resident); optionally the reference-layout normalised f32 mel.
+int wt_engine::log_mel(const float* pcm, int n_clips, int n_samples, int pcm_mem, float* out, int out_mem,
+                       bool finalize) {
+  if (!filters_set) return fail(WT_ERR_STATE, "wt_set_mel_filters has not been called");
+  if (n_clips < 1 || n_clips > max_batch) return fail(WT_ERR_INVALID, "n_clips %d outside [1, max_batch=%d]", n_clips, max_batch);
+  if (n_samples < wt::kHop || n_samples > WT_N_SAMPLES) return fail(WT_ERR_INVALID, "n_samples %d outside [160, 480000]", n_samples);
+  if (!pcm) return fail(WT_ERR_INVALID, "pcm is null");
+  const float* src = pcm;
+  if (pcm_mem == WT_HOST) {
+    WT_CUDA_OK(cudaMemcpyAsync(d_pcm, pcm, (size_t)n_clips * n_samples * 4, cudaMemcpyHostToDevice, stream));
+    src = d_pcm;
+  }
+  const int n_len = n_samples / wt::kHop;
+  wt::fill_int_kernel<<<(n_clips + 255) / 256, 256, 0, stream>>>(d_clip_max, INT_MIN, n_clips);
+  WT_TRY(check_launch("fill_int_kernel"));
+  wt::MelParams p{};
+  p.pcm = src;
+  p.raw = d_mel_raw;
+  p.clip_max = d_clip_max;
+  p.hann = d_hann;
+  p.tw400 = (const float2*)d_tw400;
+  p.fw = d_fw;
+  p.frow = (const int2*)d_frow;
+  p.flen = d_flen;
+  p.n_samples = n_samples;
+  p.n_len = n_len;
+  p.n_mel = n_mel;
+  p.n_tiles = (n_len + wt::kTileFrames - 1) / wt::kTileFrames;
+  wt::mel_frames_kernel<<<dim3(p.n_tiles, n_clips), wt::kMelThreads, wt::kMelSmemBytes, stream>>>(p);
+  WT_TRY(check_launch("mel_frames_kernel"));
+  mel_clips = n_clips;
+  mel_len = n_len;
+  if (finalize) {
+    wt::mel_finalize_f32_kernel<<<num_sms * 4, 256, 0, stream>>>(d_mel_raw, d_clip_max, d_mel, n_mel * n_len, n_clips);
+    WT_TRY(check_launch("mel_finalize_f32_kernel"));
+    if (out)
+      WT_CUDA_OK(cudaMemcpyAsync(out, d_mel, (size_t)n_clips * n_mel * n_len * 4,
+                                 out_mem == WT_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, stream));
+  }
+  if (pcm_mem == WT_HOST || (out && out_mem == WT_HOST)) WT_CUDA_OK(cudaStreamSynchronize(stream));
+  return WT_OK;
+}
+
+int wt_engine::load_model(const char* path) {
+  WeightFile wf;
+  WT_TRY(wf.open(path));
+  dims = wf.dims;
+  const int d = dims.d_model, H = dims.n_heads, V = dims.n_vocab, S = dims.n_audio_ctx;
+  if (d % 64 != 0 || H * 64 != d || d > 1024) return fail(WT_ERR_FORMAT, "unsupported dims: d_model=%d heads=%d (head_dim must be 64)", d, H);
+  if (dims.n_mels != 80 || S != 1500) return fail(WT_ERR_FORMAT, "unsupported n_mels=%d n_audio_ctx=%d", dims.n_mels, S);
+  if (dims.n_text_ctx < 32) return fail(WT_ERR_FORMAT, "n_text_ctx too small");
+  esz = f32mode() ? 4 : 2;
+  const size_t B = (size_t)max_batch;
+
+  auto up_lin = [&](Lin& L, const std::vector<float>& w, const std::vector<float>* b, int N, int K) -> int {
+    L.N = N;
+    L.K = K;
+    WT_TRY(upload_T(&L.w, w.data(), w.size()));
+    if (b) WT_TRY(upload_f32(&L.b, b->data(), b->size()));
+    return WT_OK;
+  };
+  auto get = [&](const std::string& n, std::initializer_list<int64_t> shp) { return wf.find(n, shp); };
+  auto vec = [](const HostTensor* t) { return std::vector<float>(t->data, t->data + t->numel()); };
+  auto up_ln = [&](LNp& ln, const std::string& pfx) -> int {
+    const HostTensor *g = get(pfx + ".weight", {d}), *b = get(pfx + ".bias", {d});
+    if (!g || !b) return WT_ERR_FORMAT;
+    WT_TRY(upload_f32(&ln.g, g->data, d));
+    WT_TRY(upload_f32(&ln.b, b->data, d));
+    return WT_OK;
+  };
+  // conv weights [n][c][3] -> [n][tap][c]
+  auto up_conv = [&](Lin& L, const std::string& pfx, int cin) -> int {
+    const HostTensor *w = get(pfx + ".weight", {d, cin, 3}), *b = get(pfx + ".bias", {d});
+    if (!w || !b) return WT_ERR_FORMAT;
+    std::vector<float> p((size_t)d * 3 * cin);
+    for (int n = 0; n < d; ++n)
+      for (int c = 0; c < cin; ++c)
+        for (int k = 0; k < 3; ++k) p[((size_t)n * 3 + k) * cin + c] = w->data[((size_t)n * cin + c) * 3 + k];
+    std::vector<float> bb = vec(b);
+    return up_lin(L, p, &bb, d, 3 * cin);
+  };
+  auto up_plain = [&](Lin& L, const std::string& pfx, int N, int K, bool bias) -> int {
+    const HostTensor* w = get(pfx + ".weight", {N, K});
+    if (!w) return WT_ERR_FORMAT;
+    std::vector<float> ww = vec(w);
+    if (bias) {
+      const HostTensor* b = get(pfx + ".bias", {N});
+      if (!b) return WT_ERR_FORMAT;
+      std::vector<float> bb = vec(b);
+      return up_lin(L, ww, &bb, N, K);
+    }
+    return up_lin(L, ww, nullptr, N, K);
+  };
+  // fused q|k|v (k has no bias -> zeros) or k|v
+  auto up_fused = [&](Lin& L, const std::string& pfx, bool with_q) -> int {
+    const HostTensor *qw = get(pfx + ".query.weight", {d, d}), *qb = get(pfx + ".query.bias", {d});
+    const HostTensor *kw = get(pfx + ".key.weight", {d, d});
+    const HostTensor *vw = get(pfx + ".value.weight", {d, d}), *vb = get(pfx + ".value.bias", {d});
+    if (!qw || !qb || !kw || !vw || !vb) return WT_ERR_FORMAT;
+    std::vector<float> w, b;
+    if (with_q) {
+      w.insert(w.end(), qw->data, qw->data + (size_t)d * d);
+      b.insert(b.end(), qb->data, qb->data + d);
+    }
+    w.insert(w.end(), kw->data, kw->data + (size_t)d * d);
+    b.insert(b.end(), (size_t)d, 0.0f);
+    w.insert(w.end(), vw->data, vw->data + (size_t)d * d);
+    b.insert(b.end(), vb->data, vb->data + d);
+    return up_lin(L, w, &b, with_q ? 3 * d : 2 * d, d);
+  };
+
+  WT_TRY(up_conv(conv1, "encoder.conv1", dims.n_mels));
+  WT_TRY(up_conv(conv2, "encoder.conv2", d));
+  {
+    const HostTensor* pe = get("encoder.positional_embedding", {S, d});
+    if (!pe) return WT_ERR_FORMAT;
+    WT_TRY(upload_T(&enc_pos, pe->data, (size_t)S * d));
+    if (f32mode()) enc_pos_f32 = (float*)enc_pos;
+  }
+  enc.resize(dims.n_enc_layers);
+  for (int i = 0; i < dims.n_enc_layers; ++i) {
+    const std::string p = "encoder.blocks." + std::to_string(i);
+    WT_TRY(up_ln(enc[i].ln1, p + ".attn_ln"));
+    WT_TRY(up_fused(enc[i].qkv, p + ".attn", true));
+    WT_TRY(up_plain(enc[i].out, p + ".attn.out", d, d, true));
+    WT_TRY(up_ln(enc[i].ln2, p + ".mlp_ln"));
+    WT_TRY(up_plain(enc[i].fc1, p + ".mlp.0", 4 * d, d, true));
+    WT_TRY(up_plain(enc[i].fc2, p + ".mlp.2", d, 4 * d, true));
+  }
+  WT_TRY(up_ln(ln_post, "encoder.ln_post"));
+  {
+    const HostTensor *te = get("decoder.token_embedding.weight", {V, d}), *pe = get("decoder.positional_embedding", {dims.n_text_ctx, d});
+    if (!te || !pe) return WT_ERR_FORMAT;
+    WT_TRY(upload_T(&tok_emb, te->data, (size_t)V * d));
+    WT_TRY(upload_T(&dec_pos, pe->data, (size_t)dims.n_text_ctx * d));
+  }
+  dec.resize(dims.n_dec_layers);
+  const size_t kv_elems = B * (size_t)H * S * 64;
+  const size_t cache_elems = B * (size_t)H * 32 * 64;
+  for (int i = 0; i < dims.n_dec_layers; ++i) {
+    const std::string p = "decoder.blocks." + std::to_string(i);
+    DecLayer& L = dec[i];
+    WT_TRY(up_ln(L.ln1, p + ".attn_ln"));
+    WT_TRY(up_fused(L.qkv, p + ".attn", true));
+    WT_TRY(up_plain(L.out, p + ".attn.out", d, d, true));
+    WT_TRY(up_ln(L.lnx, p + ".cross_attn_ln"));
+    WT_TRY(up_plain(L.xq, p + ".cross_attn.query", d, d, true));
+    WT_TRY(up_fused(L.xkv, p + ".cross_attn", false));
+    WT_TRY(up_plain(L.xout, p + ".cross_attn.out", d, d, true));
+    WT_TRY(up_ln(L.ln2, p + ".mlp_ln"));
+    WT_TRY(up_plain(L.fc1, p + ".mlp.0", 4 * d, d, true));
+    WT_TRY(up_plain(L.fc2, p + ".mlp.2", d, 4 * d, true));
+    WT_TRY(alloc_bytes(&L.kx, kv_elems * esz));
+    WT_TRY(alloc_bytes(&L.vx, kv_elems * esz));
+    WT_TRY(alloc_bytes(&L.kc, cache_elems * esz, true));
+    WT_TRY(alloc_bytes(&L.vc, cache_elems * esz, true));
+  }
+  WT_TRY(up_ln(dec_ln, "decoder.ln"));
+
+  const size_t rows = B * S;
+  WT_TRY(alloc_bytes(&mel_tm, B * (WT_N_FRAMES + 2) * dims.n_mels * esz, true));
+  WT_TRY(alloc_bytes(&x1, B * (WT_N_FRAMES + 2) * d * esz, true));
+  WT_TRY(alloc_bytes(&x, rows * d * esz));
+  WT_TRY(alloc_bytes(&xn, rows * d * esz));
+  WT_TRY(alloc_bytes(&att, rows * d * esz));
+  WT_TRY(alloc_bytes(&qkv, rows * 3 * d * esz));
+  WT_TRY(alloc_bytes(&hbuf, rows * 4 * d * esz));
+  WT_TRY(alloc_bytes(&enc_out, rows * d * esz));
+  WT_TRY(alloc_bytes(&dx, B * d * esz));
+  WT_TRY(alloc_bytes(&dxn, B * d * esz));
+  WT_TRY(alloc_bytes(&datt, B * d * esz));
+  WT_TRY(alloc_bytes(&dqkv, B * 3 * d * esz));
+  WT_TRY(alloc_bytes(&dq, B * d * esz));
+  WT_TRY(alloc_bytes(&dh, B * 4 * d * esz));
+  WT_TRY(alloc(&logits, B * V));
+  if (keep_logits) WT_TRY(alloc(&step_logits, (size_t)(WT_MAX_TOKENS - 1) * B * V));
+  WT_TRY(alloc(&xa_part, B * H * wt::kXaMaxSplit * 66));
+  WT_TRY(alloc(&xa_tickets, B * H, true));
+  WT_TRY(alloc(&argmax_part, B * ((V + 63) / 64)));
+  WT_TRY(alloc(&tokens, B * 32));
+  WT_TRY(alloc(&lens, B));
+  WT_TRY(alloc(&done, B));
+  WT_TRY(alloc(&d_prompt, 32));
+  has_model = true;
+  return WT_OK;
+}
+
+// mel -> encoder states (+ cross-attention K/V of every decoder layer), all resident.
+int wt_engine::encode(const float* mel, int n_clips, int mel_mem, float* states_out, int out_mem, bool from_raw) {
+  if (!has_model) return fail(WT_ERR_STATE, "engine was created without weights");
+  if (n_clips < 1 || n_clips > max_batch) return fail(WT_ERR_INVALID, "n_clips %d outside [1, max_batch=%d]", n_clips, max_batch);
+  const int d = dims.d_model, H = dims.n_heads, S = dims.n_audio_ctx, T = WT_N_FRAMES, nm = dims.n_mels;
+  const float* src = nullptr;
+  const int* cmax = nullptr;
+  if (mel) {
+    src = mel;
+    if (mel_mem == WT_HOST) {
+      WT_CUDA_OK(cudaMemcpyAsync(d_mel, mel, (size_t)n_clips * nm * T * 4, cudaMemcpyHostToDevice, stream));
+      src = d_mel;
+    }
+  } else {
+    if (mel_clips < n_clips || mel_len != T)
+      return fail(WT_ERR_STATE, "no resident mel for %d clips of 3000 frames (call wt_log_mel on 480000-sample clips first)", n_clips);
+    src = from_raw ? d_mel_raw : d_mel;
+    cmax = from_raw ? d_clip_max : nullptr;
+  }
+  // [B][80][3000] f32 -> zero-padded time-major [B][3002][80] (clamp + affine fused when reading raw)
+  {
+    dim3 grid((T + 31) / 32, (nm + 31) / 32, n_clips);
+    if (f32mode())
+      wt::mel_to_time_major_kernel<float><<<grid, 256, 0, stream>>>(src, cmax, (float*)mel_tm, nm, T);
+    else
+      wt::mel_to_time_major_kernel<bf16><<<grid, 256, 0, stream>>>(src, cmax, (bf16*)mel_tm, nm, T);
+    WT_TRY(check_launch("mel_to_time_major_kernel"));
+  }
+  const int M1 = n_clips * T, M2 = n_clips * S;
+  if (f32mode()) {
+    wt::GemmF32Params p{};
+    // conv1 + GELU -> interior rows of x1
+    p.A = (const float*)mel_tm;
+    p.amap = RowMap{(long long)(T + 2) * nm, T, nm};
+    p.W = (const float*)conv1.w;
+    p.bias = conv1.b;
+    p.C = (float*)x1 + d;
+    p.cmap = RowMap{(long long)(T + 2) * d, T, d};
+    p.rmap = p.cmap;
+    p.pos_rows = 1;
+    p.M = M1;
+    p.N = d;
+    p.K = 3 * nm;
+    p.flags = wt::EPI_BIAS | wt::EPI_GELU;
+    wt::sgemm_f32_kernel<<<dim3((d + 63) / 64, (M1 + 63) / 64), 256, 0, stream>>>(p);
+    WT_TRY(check_launch("sgemm_f32_kernel(conv1)"));
+    // conv2 (stride 2) + GELU + positional rows -> x
+    wt::GemmF32Params q{};
+    q.A = (const float*)x1;
+    q.amap = RowMap{(long long)(T + 2) * d, S, 2 * d};
+    q.W = (const float*)conv2.w;
+    q.bias = conv2.b;
+    q.pos = enc_pos_f32;
+    q.pos_rows = S;
+    q.C = (float*)x;
+    q.cmap = RowMap{0, M2, d};
+    q.rmap = q.cmap;
+    q.M = M2;
+    q.N = d;
+    q.K = 3 * d;
+    q.flags = wt::EPI_BIAS | wt::EPI_GELU | wt::EPI_POS;
+    wt::sgemm_f32_kernel<<<dim3((d + 63) / 64, (M2 + 63) / 64), 256, 0, stream>>>(q);
+    WT_TRY(check_launch("sgemm_f32_kernel(conv2)"));
+  } else {
+    {
+      const uint64_t ad[3] = {(uint64_t)nm, (uint64_t)(T + 2), (uint64_t)n_clips};
+      const uint64_t as[2] = {(uint64_t)nm * 2, (uint64_t)(T + 2) * nm * 2};
+      const int c0[3] = {0, 0, 0}, r0[3] = {0, 1, 2};
+      WT_TRY(gemm_bf16(mel_tm, ad, as, T, n_clips, conv1, 3 * nm, 3, nm, c0, r0, (bf16*)x1 + d,
+                       RowMap{(long long)(T + 2) * d, T, d}, wt::EPI_GELU, nullptr, RowMap{0, 1, 0}, nullptr));
+    }
+    {
+      // rows of the map are PAIRS of padded time steps: pair p holds steps 2p, 2p+1 (2d elements)
+      const uint64_t ad[3] = {(uint64_t)2 * d, (uint64_t)(T + 2) / 2, (uint64_t)n_clips};
+      const uint64_t as[2] = {(uint64_t)2 * d * 2, (uint64_t)(T + 2) * d * 2};
+      const int c0[3] = {0, d, 0}, r0[3] = {0, 0, 1};
+      WT_TRY(gemm_bf16(x1, ad, as, S, n_clips, conv2, 3 * d, 3, d, c0, r0, x, RowMap{0, M2, d},
+                       wt::EPI_GELU | wt::EPI_ADD, enc_pos, RowMap{0, S, d}, nullptr));
+    }
+  }
+  for (int l = 0; l < dims.n_enc_layers; ++l) {
+    EncLayer& L = enc[l];
+    WT_TRY(layernorm(x, L.ln1, xn, M2));
+    WT_TRY(linear(xn, M2, L.qkv, qkv, 0));
+    if (f32mode()) {
+      wt::attention_simt_kernel<float><<<dim3((S + 127) / 128, H, n_clips), 128, 0, stream>>>((const float*)qkv, (float*)att, S, H);
+      WT_TRY(check_launch("attention_simt_kernel"));
+    } else {
+      wt::attention_simt_kernel<bf16><<<dim3((S + 127) / 128, H, n_clips), 128, 0, stream>>>((const bf16*)qkv, (bf16*)att, S, H);
+      WT_TRY(check_launch("attention_simt_kernel"));
+    }
+    WT_TRY(linear(att, M2, L.out, x, 0, x));
+    WT_TRY(layernorm(x, L.ln2, xn, M2));
+    WT_TRY(linear(xn, M2, L.fc1, hbuf, wt::EPI_GELU));
+    WT_TRY(linear(hbuf, M2, L.fc2, x, 0, x));
+  }
+  WT_TRY(layernorm(x, ln_post, enc_out, M2));
+  // cross-attention K/V of every decoder layer, once per clip (the reference recomputes them inside every
+  // decoder Invoke: whisper.cpp:375)
+  for (int l = 0; l < dims.n_dec_layers; ++l) {
+    DecLayer& L = dec[l];
+    WT_TRY(linear(enc_out, M2, L.xkv, qkv, 0));
+    if (f32mode())
+      wt::split_heads_kv_kernel<float><<<num_sms * 4, 256, 0, stream>>>((const float*)qkv, (float*)L.kx, (float*)L.vx, n_clips, S, H);
+    else
+      wt::split_heads_kv_kernel<bf16><<<num_sms * 4, 256, 0, stream>>>((const bf16*)qkv, (bf16*)L.kx, (bf16*)L.vx, n_clips, S, H);
+    WT_TRY(check_launch("split_heads_kv_kernel"));
+  }
+  enc_clips = n_clips;
+  if (states_out) {
+    const size_t n = (size_t)M2 * d;
+    float* dst = states_out;
+    if (f32mode()) {
+      WT_CUDA_OK(cudaMemcpyAsync(dst, enc_out, n * 4, out_mem == WT_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, stream));
+    } else {
+      float* tmp = states_out;
+      if (out_mem == WT_HOST) {
+        if (!io_f32) WT_TRY(alloc(&io_f32, (size_t)max_batch * S * d));
+        tmp = io_f32;
+      }
+      wt::convert_kernel<bf16, float><<<num_sms * 4, 256, 0, stream>>>((const bf16*)enc_out, tmp, (long long)n);
+      WT_TRY(check_launch("convert_kernel"));
+      if (out_mem == WT_HOST) WT_CUDA_OK(cudaMemcpyAsync(dst, tmp, n * 4, cudaMemcpyDeviceToHost, stream));
+    }
+  }
+  if ((mel && mel_mem == WT_HOST) || (states_out && out_mem == WT_HOST)) WT_CUDA_OK(cudaStreamSynchronize(stream));
+  return WT_OK;
+}
+
+template <class T>
+static int decode_step_attn(wt_engine* e, DecLayer& L, int n_clips, int pos, bool cross) {
+  const int H = e->dims.n_heads, S = e->dims.n_audio_ctx;
+  if (!cross) {
+    wt::decode_self_attn_kernel<T><<<dim3(H, n_clips), 64, 0, e->stream>>>((const T*)e->dqkv, (T*)L.kc, (T*)L.vc, (T*)e->datt, pos, 32, H);
+    return e->check_launch("decode_self_attn_kernel");
+  }
+  // enough splits to put >= 2 CTAs on every SM
+  int nsplit = (2 * e->num_sms + n_clips * H - 1) / (n_clips * H);
+  if (nsplit < 1) nsplit = 1;
+  if (nsplit > wt::kXaMaxSplit) nsplit = wt::kXaMaxSplit;
+  wt::decode_cross_attn_kernel<T><<<dim3(nsplit, H, n_clips), 128, 0, e->stream>>>((const T*)e->dq, (const T*)L.kx, (const T*)L.vx, (T*)e->datt,
+                                                                                   e->xa_part, e->xa_tickets, S, H);
+  return e->check_launch("decode_cross_attn_kernel");
+}
+
+// Greedy loop of Decoder::forward (whisper.cpp:363-402) over the resident encoder states, one new position per
+// step with a KV cache; per-clip `done` flags replace the reference's early break.
+int wt_engine::decode(int n_clips, const int64_t* prompt, int prompt_len, int max_total, int64_t eot, int32_t* ids,
+                      int32_t* lens_o, int out_mem) {
+  if (!has_model) return fail(WT_ERR_STATE, "engine was created without weights");
+  if (n_clips < 1 || n_clips > enc_clips) return fail(WT_ERR_STATE, "encoder states resident for %d clips, decode asked for %d", enc_clips, n_clips);
+  if (!prompt || prompt_len < 1 || prompt_len > max_total || max_total > 32 || max_total < 2)
+    return fail(WT_ERR_INVALID, "need 1 <= prompt_len <= max_total_tokens <= 32");
+  if (!ids || !lens_o) return fail(WT_ERR_INVALID, "ids_out / lens_out are null");
+  const int d = dims.d_model, V = dims.n_vocab;
+  int hp[32];
+  for (int i = 0; i < prompt_len; ++i) {
+    if (prompt[i] < 0 || prompt[i] >= V) return fail(WT_ERR_INVALID, "prompt token %lld outside the vocabulary", (long long)prompt[i]);
+    hp[i] = (int)prompt[i];
+  }
+  WT_CUDA_OK(cudaMemcpyAsync(d_prompt, hp, prompt_len * 4, cudaMemcpyHostToDevice, stream));
+  wt::init_decode_state_kernel<<<n_clips, 32, 0, stream>>>(d_prompt, prompt_len, tokens, 32, lens, done);
+  WT_TRY(check_launch("init_decode_state_kernel"));
+  Lin logit_lin;
+  logit_lin.w = tok_emb;
+  logit_lin.b = nullptr;
+  logit_lin.N = V;
+  logit_lin.K = d;
+  // position `pos` = index of the last token fed; the reference feeds i+1 tokens for i = prompt_len-1 .. 29 and
+  // appends one (whisper.cpp:367-395), so positions 0 .. max_total-2 are consumed and logits start at prompt_len-1.
+  for (int pos = 0; pos <= max_total - 2; ++pos) {
+    if (f32mode())
+      wt::embed_kernel<float><<<n_clips, 128, 0, stream>>>(tokens, 32, pos, (const float*)tok_emb, (const float*)dec_pos, (float*)dx, d);
+    else
+      wt::embed_kernel<bf16><<<n_clips, 128, 0, stream>>>(tokens, 32, pos, (const bf16*)tok_emb, (const bf16*)dec_pos, (bf16*)dx, d);
+    WT_TRY(check_launch("embed_kernel"));
+    for (int l = 0; l < dims.n_dec_layers; ++l) {
+      DecLayer& L = dec[l];
+      WT_TRY(layernorm(dx, L.ln1, dxn, n_clips));
+      WT_TRY(linear(dxn, n_clips, L.qkv, dqkv, 0));
+      WT_TRY(f32mode() ? decode_step_attn<float>(this, L, n_clips, pos, false) : decode_step_attn<bf16>(this, L, n_clips, pos, false));
+      WT_TRY(linear(datt, n_clips, L.out, dx, 0, dx));
+      WT_TRY(layernorm(dx, L.lnx, dxn, n_clips));
+      WT_TRY(linear(dxn, n_clips, L.xq, dq, 0));
+      WT_TRY(f32mode() ? decode_step_attn<float>(this, L, n_clips, pos, true) : decode_step_attn<bf16>(this, L, n_clips, pos, true));
+      WT_TRY(linear(datt, n_clips, L.xout, dx, 0, dx));
+      WT_TRY(layernorm(dx, L.ln2, dxn, n_clips));
+      WT_TRY(linear(dxn, n_clips, L.fc1, dh, wt::EPI_GELU));
+      WT_TRY(linear(dh, n_clips, L.fc2, dx, 0, dx));
+    }
+    if (pos < prompt_len - 1) continue;
+    WT_TRY(layernorm(dx, dec_ln, dxn, n_clips));
+    const int step = pos - (prompt_len - 1);
+    if (f32mode() || keep_logits) {
+      float* lg = keep_logits ? step_logits + (size_t)step * max_batch * V : logits;
+      if (f32mode()) {
+        WT_TRY(linear(dxn, n_clips, logit_lin, lg, 0));
+      } else {
+        const uint64_t ad[3] = {(uint64_t)d, (uint64_t)n_clips, 1};
+        const uint64_t as[2] = {(uint64_t)d * 2, (uint64_t)d * 2 * n_clips};
+        WT_TRY(gemm_bf16(dxn, ad, as, n_clips, 1, logit_lin, d, 1, 0, nullptr, nullptr, lg, RowMap{0, n_clips, V},
+                         wt::EPI_OUT_F32, nullptr, RowMap{0, 1, 0}, nullptr));
+      }
+      wt::argmax_append_kernel<<<n_clips, 256, 0, stream>>>(lg, V, tokens, 32, lens, done, pos, (int)eot);
+      WT_TRY(check_launch("argmax_append_kernel"));
+    } else {
+      // fused: per-(row, N-tile) (max, last index) in the GEMM epilogue, logits never reach HBM
+      const int bn = 128, n_part = (V + bn - 1) / bn;
+      const uint64_t ad[3] = {(uint64_t)d, (uint64_t)n_clips, 1};
+      const uint64_t as[2] = {(uint64_t)d * 2, (uint64_t)d * 2 * n_clips};
+      WT_TRY(gemm_bf16(dxn, ad, as, n_clips, 1, logit_lin, d, 1, 0, nullptr, nullptr, nullptr, RowMap{0, n_clips, V},
+                       wt::EPI_ARGMAX, nullptr, RowMap{0, 1, 0}, argmax_part, bn));
+      wt::argmax_partials_kernel<<<n_clips, 128, 0, stream>>>(argmax_part, n_part, tokens, 32, lens, done, pos, (int)eot);
+      WT_TRY(check_launch("argmax_partials_kernel"));
+    }
+  }
+  // results: [n_clips][max_total] ids (tokens has stride 32), lens
+  if (out_mem == WT_HOST) {
+    std::vector<int> ht((size_t)n_clips * 32), hl(n_clips);
+    WT_CUDA_OK(cudaMemcpyAsync(ht.data(), tokens, ht.size() * 4, cudaMemcpyDeviceToHost, stream));
+    WT_CUDA_OK(cudaMemcpyAsync(hl.data(), lens, hl.size() * 4, cudaMemcpyDeviceToHost, stream));
+    WT_CUDA_OK(cudaStreamSynchronize(stream));
+    for (int b = 0; b < n_clips; ++b) {
+      for (int i = 0; i < max_total; ++i) ids[(size_t)b * max_total + i] = ht[(size_t)b * 32 + i];
+      lens_o[b] = hl[b];
+    }
+  } else {
+    WT_CUDA_OK(cudaMemcpy2DAsync(ids, (size_t)max_total * 4, tokens, 32 * 4, (size_t)max_total * 4, n_clips, cudaMemcpyDeviceToDevice, stream));
+    WT_CUDA_OK(cudaMemcpyAsync(lens_o, lens, (size_t)n_clips * 4, cudaMemcpyDeviceToDevice, stream));
+  }
+  return WT_OK;
+}
+
+// ================================================================================================
+// C ABI
+// ================================================================================================
+extern "C" {
+
+const char* wt_last_error(void) { return g_err; }
+const char* wt_version(void) { return "whisper_b200 0.1 (sm_100a)"; }
+
+int wt_engine_create(const wt_config* cfg, const char* weights_path, int device, wt_engine** out) {
+  if (!out) return fail(WT_ERR_INVALID, "out is null");
+  *out = nullptr;
+  if (!cfg || cfg->struct_size != (int32_t)sizeof(wt_config)) return fail(WT_ERR_INVALID, "wt_config.struct_size mismatch");
+  if (cfg->max_batch < 1 || cfg->max_batch > 4096) return fail(WT_ERR_INVALID, "max_batch outside [1, 4096]");
+  if (cfg->precision != WT_PRECISION_BF16 && cfg->precision != WT_PRECISION_FP32_VERIFY) return fail(WT_ERR_INVALID, "unknown precision");
+  int n_dev = 0;
+  if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev < 1) return fail(WT_ERR_CUDA, "no CUDA device visible: this library has no CPU path");
+  if (device < 0 || device >= n_dev) return fail(WT_ERR_INVALID, "device %d outside [0, %d)", device, n_dev);
+  WT_CUDA_OK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  WT_CUDA_OK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) return fail(WT_ERR_CUDA, "device %d is sm_%d%d; this build is sm_100a only", device, prop.major, prop.minor);
+  wt_engine* e = new wt_engine();
+  e->device = device;
+  e->precision = cfg->precision;
+  e->max_batch = cfg->max_batch;
+  e->keep_logits = cfg->keep_logits;
+  e->num_sms = prop.multiProcessorCount;
+  int st = WT_OK;
+  if (cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking) != cudaSuccess) st = fail(WT_ERR_CUDA, "cudaStreamCreate failed");
+  e->stream = e->own_stream;
+  if (st == WT_OK) st = e->init_frontend();
+  if (st == WT_OK && weights_path) st = e->load_model(weights_path);
+  if (st == WT_OK && cudaDeviceSynchronize() != cudaSuccess) st = fail(WT_ERR_CUDA, "device sync after load failed");
+  if (st != WT_OK) {
+    delete e;
+    return st;
+  }
+  *out = e;
+  return WT_OK;
+}
+
+void wt_engine_destroy(wt_engine* e) { delete e; }
+
+int wt_engine_dims(const wt_engine* e, wt_dims* out) {
+  if (!e || !out) return fail(WT_ERR_INVALID, "null argument");
+  if (!e->has_model) return fail(WT_ERR_STATE, "engine was created without weights");
+  *out = e->dims;
+  return WT_OK;
+}
+
+int wt_set_mel_filters(wt_engine* e, const float* filters, int n_mel, int n_freq) {
+  if (!e) return fail(WT_ERR_INVALID, "engine is null");
+  cudaSetDevice(e->device);
+  return e->set_filters(filters, n_mel, n_freq);
+}
+
+int wt_set_stream(wt_engine* e, void* s) {
+  if (!e) return fail(WT_ERR_INVALID, "engine is null");
+  e->stream = s ? (cudaStream_t)s : e->own_stream;
+  return WT_OK;
+}
+
+int wt_synchronize(wt_engine* e) {
+  if (!e) return fail(WT_ERR_INVALID, "engine is null");
+  cudaSetDevice(e->device);
+  WT_CUDA_OK(cudaStreamSynchronize(e->stream));
+  return WT_OK;
+}
+
+int wt_log_mel(wt_engine* e, const float* pcm, int n_clips, int n_samples, int pcm_mem, float* mel_out, int out_mem) {
+  if (!e) return fail(WT_ERR_INVALID, "engine is null");
+  cudaSetDevice(e->device);
+  return e->log_mel(pcm, n_clips, n_samples, pcm_mem, mel_out, out_mem, true);
+}
+
+int wt_encode(wt_engine* e, const float* mel, int n_clips, int mel_mem, float* states_out, int out_mem) {
+  if (!e) return fail(WT_ERR_INVALID, "engine is null");
+  cudaSetDevice(e->device);
+  return e->encode(mel, n_clips, mel_mem, states_out, out_mem, false);
+}
+
+int wt_decode_greedy(wt_engine* e, int n_clips, const int64_t* prompt, int prompt_len, int max_total_tokens, int64_t eot,
+                     int32_t* ids_out, int32_t* lens_out, int out_mem) {
+  if (!e) return fail(WT_ERR_INVALID, "engine is null");
+  cudaSetDevice(e->device);
+  return e->decode(n_clips, prompt, prompt_len, max_total_tokens, eot, ids_out, lens_out, out_mem);
+}
+
+int wt_transcribe_tokens(wt_engine* e, const float* pcm, int n_clips, int n_samples, int pcm_mem, const int64_t* prompt,
+                         int prompt_len, int max_total_tokens, int64_t eot, int32_t* ids_out, int32_t* lens_out,
+                         int out_mem) {
+  if (!e) return fail(WT_ERR_INVALID, "engine is null");
+  cudaSetDevice(e->device);
+  if (n_samples != WT_N_SAMPLES) return fail(WT_ERR_INVALID, "wt_transcribe_tokens needs 480000-sample windows (pad/trim like whisper.cpp:753)");
+  WT_TRY(e->log_mel(pcm, n_clips, n_samples, pcm_mem == WT_HOST ? WT_HOST : WT_DEVICE, nullptr, WT_DEVICE, false));
+  WT_TRY(e->encode(nullptr, n_clips, WT_DEVICE, nullptr, WT_DEVICE, true));
+  return e->decode(n_clips, prompt, prompt_len, max_total_tokens, eot, ids_out, lens_out, out_mem);
+}
+
+int wt_get_step_logits(wt_engine* e, int step, int n_clips, float* out, int out_mem) {
+  if (!e || !out) return fail(WT_ERR_INVALID, "null argument");
+  if (!e->keep_logits || !e->step_logits) return fail(WT_ERR_STATE, "engine was not created with keep_logits");
+  if (step < 0 || step >= WT_MAX_TOKENS - 1 || n_clips < 1 || n_clips > e->max_batch) return fail(WT_ERR_INVALID, "bad step / n_clips");
+  cudaSetDevice(e->device);
+  const size_t V = e->dims.n_vocab;
+  WT_CUDA_OK(cudaMemcpyAsync(out, e->step_logits + (size_t)step * e->max_batch * V, (size_t)n_clips * V * 4,
+                             out_mem == WT_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, e->stream));
+  WT_CUDA_OK(cudaStreamSynchronize(e->stream));
+  return WT_OK;
+}
+
+int64_t wt_launch_count(const wt_engine* e) { return e ? e->launches : 0; }
+
+int wt_debug_gemm_bf16(void* cuda_stream, const void* A, const void* W, const float* bias, void* C, int M, int N, int K,
+                       int flags) {
+  if (!A || !W || !C || M < 1 || N < 8 || K < 8 || (K % 8) || (N % 8)) return fail(WT_ERR_INVALID, "bad GEMM arguments");
+  static thread_local wt_engine* scratch = nullptr;
+  int dev = 0;
+  WT_CUDA_OK(cudaGetDevice(&dev));
+  if (!scratch || scratch->device != dev) {
+    cudaDeviceProp prop;
+    WT_CUDA_OK(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major != 10) return fail(WT_ERR_CUDA, "sm_100a only");
+    scratch = new wt_engine();
+    scratch->device = dev;
+    scratch->num_sms = prop.multiProcessorCount;
+  }
+  scratch->stream = (cudaStream_t)cuda_stream;
+  scratch->precision = WT_PRECISION_BF16;
+  Lin L;
+  L.w = const_cast<void*>(W);
+  L.b = const_cast<float*>(bias);
+  L.N = N;
+  L.K = K;
+  return scratch->linear(A, M, L, C, flags & wt::EPI_GELU);
+}
+
+}  // extern "C"

@@ -1,0 +1,435 @@
+// bf16 tensor-core GEMM for sm_100a: C = epi(A . W^T), f32 accumulate in TMEM.
+//
+// Every dense contraction of the Whisper graph that the reference runs inside
+// tflite::Interpreter::Invoke (whisper.cpp:295, :375 — CONV_2D / FULLY_CONNECTED per
+// export/generate_onnx.py:85-130) goes through this one kernel: conv1/conv2 (as GEMMs over overlapping
+// rows of a zero-padded time-major activation), QKV, attention out-proj, MLP fc1/fc2, the cross-attention
+// K/V projection, and the decoder's per-step projections and tied logits.
+//
+// Structure (one CTA per SM, persistent over output tiles, 6 warps):
+//   warp 0      TMA producer: cp.async.bulk.tensor loads of A [128 x 64] and W [BN x 64] bf16 tiles,
+//               128B-swizzled, into a kStages-deep ring guarded by full/empty mbarriers;
+//   warp 1      TMEM allocator + MMA issuer: one elected lane issues tcgen05.mma.cta_group::1.kind::f16
+//               (M = 128, N = BN, K = 16) x 4 per ring slot, tcgen05.commit frees the slot / publishes the
+//               accumulator; two accumulator stages in TMEM so tile i+1's MMAs overlap tile i's epilogue;
+//   warps 2-5   epilogue: tcgen05.ld the accumulator (lane = row), + bias, erf-GELU, + addend (residual or
+//               positional rows), convert, transpose through a per-warp shared scratch so that global
+//               stores are full 128-byte row segments; or, for the logits, a fused (max, last-index)
+//               reduction per row (whisper.cpp:346-361's tie rule) instead of a store.
+// Rows are addressed through RowMap (simt_kernels.cuh) on the C/addend side and through a 3-D tensor map
+// {inner, rows, batches} on the A side, so M tiles never straddle a clip boundary and TMA's out-of-bounds
+// zero fill provides the ragged last tile and the K tail. The k=3 convolutions are "3-tap" GEMMs: the same
+// A buffer is read at three (column, row) offsets while K walks the [n][tap][c_in] weight matrix.
+#pragma once
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "simt_kernels.cuh"
+
+namespace wt {
+
+constexpr int kGemmBM = 128;
+constexpr int kGemmBK = 64;
+constexpr int kGemmThreads = 192;
+
+enum : int { EPI_ADD = 4, EPI_OUT_F32 = 16, EPI_ARGMAX = 32 };  // EPI_BIAS = 1, EPI_GELU = 2 shared with SIMT
+
+struct GemmBf16Params {
+  const float* bias;               // [N] f32 or null
+  const __nv_bfloat16* addend;     // [M][N] via amap_add (EPI_ADD) — residual stream or positional rows
+  RowMap add_map;
+  void* C;                         // bf16 (or f32 with EPI_OUT_F32) via cmap; unused with EPI_ARGMAX alone
+  RowMap cmap;
+  unsigned long long* argmax_part; // [M][n_tiles_n] packed (value, index) (EPI_ARGMAX)
+  int M, N, K;
+  int rows_per_batch;              // A-side batching (== M for a plain matrix)
+  int tiles_per_batch;             // ceil(rows_per_batch / 128)
+  int n_batches;
+  int n_tiles_n;
+  int flags;
+  // K is walked as `taps` groups of `kblocks_per_tap` 64-wide blocks. A plain GEMM has one tap. A k=3
+  // convolution over a zero-padded time-major activation has three: tap t reads the A tile at
+  // coordinates (tap_c0[t] + kc*64, row0 + tap_row[t]) and the W tile at column t*tap_k + kc*64.
+  int taps, kblocks_per_tap, tap_k;
+  int tap_c0[3], tap_row[3];
+};
+
+// ---------------------------------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P1;\n\t"
+      "WT_WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1, %2;\n\t"
+      "@P1 bra WT_WAIT_DONE;\n\t"
+      "bra WT_WAIT_LOOP;\n\t"
+      "WT_WAIT_DONE:\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity), "r"(0x989680)
+      : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t"
+      ".reg .b32 %%rx;\n\t"
+      ".reg .pred %%px;\n\t"
+      "elect.sync %%rx|%%px, %1;\n\t"
+      "@%%px mov.s32 %0, 1;\n\t"
+      "}"
+      : "+r"(pred)
+      : "r"(0xffffffffu));
+  return pred != 0;
+}
+
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1,
+                                            int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::
+          "r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// D[tmem] (+)= A[smem] . B[smem]^T, bf16 x bf16 -> f32
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on an mbarrier once all previously issued tcgen05.mma of this thread have completed
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major, 128B-swizzled operand tile whose rows are 128 bytes (64 bf16): 8-row atoms of 1024 bytes.
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);  // start address
+  d |= (uint64_t)0 << 16;                      // leading byte offset: unused for swizzled K-major
+  d |= (uint64_t)(1024 >> 4) << 32;            // stride byte offset between 8-row atoms
+  d |= (uint64_t)1 << 46;                      // descriptor version (sm_100)
+  d |= (uint64_t)2 << 61;                      // SWIZZLE_128B
+  return d;
+}
+__host__ __device__ constexpr uint32_t make_idesc_bf16(int m, int n) {
+  return (1u << 4)                    // D format f32
+         | (1u << 7)                  // A format bf16
+         | (1u << 10)                 // B format bf16
+         | ((uint32_t)(n >> 3) << 17) // N / 8
+         | ((uint32_t)(m >> 4) << 24);  // M / 16   (A, B both K-major: bits 15/16 = 0)
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+
+template <int BN>
+struct GemmSmem {
+  static constexpr int kStages = (BN <= 128) ? 6 : 4;
+  static constexpr int kABytes = kGemmBM * kGemmBK * 2;  // 16 KB
+  static constexpr int kBBytes = BN * kGemmBK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kScratchRowBytes = 128 + 16;  // 64 bf16 or 32 f32 per row + pad (keeps 16B phases conflict-free)
+  static constexpr int kScratchBytes = 4 * 32 * kScratchRowBytes;
+  static constexpr int kBiasBytes = 2 * BN * 4;
+  static constexpr int kBarBytes = (2 * kStages + 4) * 8 + 16;
+  static constexpr int kTotal = kStages * kStageBytes + kScratchBytes + kBiasBytes + kBarBytes + 1024;
+  static constexpr int kTmemCols = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
+};
+
+template <int BN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
+                       GemmBf16Params p) {
+  using S = GemmSmem<BN>;
+  extern __shared__ __align__(1024) uint8_t smem_dyn[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
+  uint8_t* s_stage = smem;
+  uint8_t* s_scratch = s_stage + S::kStages * S::kStageBytes;
+  float* s_bias = reinterpret_cast<float*>(s_scratch + S::kScratchBytes);
+  uint64_t* bar_full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(s_bias) + S::kBiasBytes);
+  uint64_t* bar_empty = bar_full + S::kStages;
+  uint64_t* bar_tfull = bar_empty + S::kStages;   // [2]
+  uint64_t* bar_tempty = bar_tfull + 2;           // [2]
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int n_tiles_m = p.tiles_per_batch * p.n_batches;
+  const int n_tiles = n_tiles_m * p.n_tiles_n;
+  const int n_kblocks = p.taps * p.kblocks_per_tap;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_w);
+    for (int i = 0; i < S::kStages; ++i) {
+      mbar_init(bar_full + i, 1);
+      mbar_init(bar_empty + i, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar_tfull + i, 1);
+      mbar_init(bar_tempty + i, 4);  // one arrive per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(s_tmem, S::kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int tn = tile % p.n_tiles_n, tm = tile / p.n_tiles_n;
+        const int batch = tm / p.tiles_per_batch, row0 = (tm % p.tiles_per_batch) * kGemmBM;
+        for (int kb = 0; kb < n_kblocks; ++kb) {
+          mbar_wait(bar_empty + stage, phase ^ 1);
+          uint8_t* sa = s_stage + stage * S::kStageBytes;
+          uint8_t* sb = sa + S::kABytes;
+          mbar_expect_tx(bar_full + stage, S::kStageBytes);
+          const int tap = kb / p.kblocks_per_tap, kc = kb - tap * p.kblocks_per_tap;
+          tma_load_3d(sa, &map_a, bar_full + stage, p.tap_c0[tap] + kc * kGemmBK, row0 + p.tap_row[tap], batch);
+          tma_load_2d(sb, &map_w, bar_full + stage, tap * p.tap_k + kc * kGemmBK, tn * BN);
+          if (++stage == S::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    constexpr uint32_t idesc = make_idesc_bf16(kGemmBM, BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(bar_tempty + acc, acc_phase ^ 1);  // epilogue has drained this accumulator
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * BN;
+      for (int kb = 0; kb < n_kblocks; ++kb) {
+        mbar_wait(bar_full + stage, phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t sa = smem_u32(s_stage + stage * S::kStageBytes);
+          const uint64_t da = make_sw128_desc(sa);
+          const uint64_t db = make_sw128_desc(sa + S::kABytes);
+#pragma unroll
+          for (int k = 0; k < kGemmBK / 16; ++k) {
+            // advance 16 bf16 = 32 bytes along K inside the swizzle atom: +2 in the (addr >> 4) field
+            umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(bar_empty + stage);                       // slot reusable once these MMAs retire
+          if (kb == n_kblocks - 1) umma_commit(bar_tfull + acc);  // accumulator complete
+        }
+        __syncwarp();
+        if (++stage == S::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    // ================= epilogue (warps 2..5) =================
+    const int ew = warp - 2;            // 0..3 (scratch slot)
+    const int lane_q = warp & 3;        // TMEM lane quarter this warp may touch: lanes 32*(warp%4)..+31
+    const int et = threadIdx.x - 64;    // 0..127
+    uint8_t* scr = s_scratch + ew * 32 * S::kScratchRowBytes;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      const int tn = tile % p.n_tiles_n, tm = tile / p.n_tiles_n;
+      const int batch = tm / p.tiles_per_batch, row0 = (tm % p.tiles_per_batch) * kGemmBM;
+      const int n0 = tn * BN;
+      float* bias_s = s_bias + acc * BN;
+      if (p.flags & EPI_BIAS)
+        for (int i = et; i < BN; i += 128) bias_s[i] = (n0 + i < p.N) ? __ldg(p.bias + n0 + i) : 0.0f;
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      mbar_wait(bar_tfull + acc, acc_phase);
+      tc_fence_after();
+      const int r_in_tile = lane_q * 32 + lane;           // accumulator row owned by this thread
+      const int r_batch = row0 + r_in_tile;               // row within the clip
+      const bool row_ok = r_batch < p.rows_per_batch;
+      const int m = batch * p.rows_per_batch + r_batch;   // logical GEMM row
+      const uint32_t t_row = tmem_base + ((uint32_t)(lane_q * 32) << 16) + acc * BN;
+      unsigned long long best = 0ull;
+
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(t_row + c0, v);
+        tmem_ld_wait();
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        if (p.flags & EPI_BIAS) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] += bias_s[c0 + j];
+        }
+        if (p.flags & EPI_GELU) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
+        }
+        if (p.flags & EPI_ADD) {
+          // coalesced fetch of this warp's 32 rows x 32 cols of the addend through the scratch
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int piece = i * 32 + lane;          // 128 pieces of 8 bf16: 4 per row
+            const int rr = piece >> 2, pc = piece & 3;
+            const int rb = row0 + lane_q * 32 + rr;
+            const int col = n0 + c0 + pc * 8;
+            uint4 val = make_uint4(0u, 0u, 0u, 0u);
+            if (rb < p.rows_per_batch && col < p.N)
+              val = *reinterpret_cast<const uint4*>(p.addend + p.add_map.at(batch * p.rows_per_batch + rb) + col);
+            *reinterpret_cast<uint4*>(scr + rr * S::kScratchRowBytes + pc * 16) = val;
+          }
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint4 val = *reinterpret_cast<const uint4*>(scr + lane * S::kScratchRowBytes + i * 16);
+            const uint32_t w[4] = {val.x, val.y, val.z, val.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              f[i * 8 + 2 * j] += __uint_as_float(w[j] << 16);
+              f[i * 8 + 2 * j + 1] += __uint_as_float(w[j] & 0xffff0000u);
+            }
+          }
+          __syncwarp();
+        }
+        if (p.flags & EPI_ARGMAX) {
+          if (row_ok) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int n = n0 + c0 + j;
+              if (n < p.N) best = u64_max(best, pack_val_idx(f[j], (unsigned)n));
+            }
+          }
+        }
+        if (p.flags & EPI_OUT_F32) {
+          // f32 output: 32 cols = 128 bytes per row
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            *reinterpret_cast<float4*>(scr + lane * S::kScratchRowBytes + i * 16) =
+                make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int piece = i * 32 + lane;  // 256 pieces of 4 f32: 8 per row
+            const int rr = piece >> 3, pc = piece & 7;
+            const int rb = row0 + lane_q * 32 + rr;
+            const int col = n0 + c0 + pc * 4;
+            if (rb < p.rows_per_batch && col < p.N) {
+              const float4 val = *reinterpret_cast<const float4*>(scr + rr * S::kScratchRowBytes + pc * 16);
+              float* dst = reinterpret_cast<float*>(p.C) + p.cmap.at(batch * p.rows_per_batch + rb) + col;
+              if (col + 3 < p.N && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+                *reinterpret_cast<float4*>(dst) = val;
+              } else {
+                const float tmp[4] = {val.x, val.y, val.z, val.w};
+                for (int q = 0; q < 4; ++q)
+                  if (col + q < p.N) dst[q] = tmp[q];
+              }
+            }
+          }
+          __syncwarp();
+        } else if (p.C != nullptr) {
+          // bf16 output: 32 cols = 64 bytes per row
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            *reinterpret_cast<uint4*>(scr + lane * S::kScratchRowBytes + i * 16) =
+                make_uint4(pack_bf16x2(f[8 * i], f[8 * i + 1]), pack_bf16x2(f[8 * i + 2], f[8 * i + 3]),
+                           pack_bf16x2(f[8 * i + 4], f[8 * i + 5]), pack_bf16x2(f[8 * i + 6], f[8 * i + 7]));
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int piece = i * 32 + lane;
+            const int rr = piece >> 2, pc = piece & 3;
+            const int rb = row0 + lane_q * 32 + rr;
+            const int col = n0 + c0 + pc * 8;
+            if (rb < p.rows_per_batch && col < p.N) {
+              const uint4 val = *reinterpret_cast<const uint4*>(scr + rr * S::kScratchRowBytes + pc * 16);
+              *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C) +
+                                        p.cmap.at(batch * p.rows_per_batch + rb) + col) = val;
+            }
+          }
+          __syncwarp();
+        }
+      }
+      // accumulator fully read: hand it back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_tempty + acc);
+      if ((p.flags & EPI_ARGMAX) && row_ok) p.argmax_part[(long long)m * p.n_tiles_n + tn] = best;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, S::kTmemCols);
+  }
+}
+
+}  // namespace wt
