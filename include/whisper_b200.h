@@ -111,6 +111,13 @@ WT_API int wt_get_step_logits(wt_engine* e, int step, int n_clips, float* out, i
 /* Number of kernel launches this engine has enqueued since creation (bench.py's gpu_launches). */
 WT_API int64_t wt_launch_count(const wt_engine* e);
 
+/* Per-stage CUDA-event profiler (events on the launching stream around every kernel launch). Enable, run
+ * calls, then read: ms_out / launches_out are arrays of wt_stage_count() entries accumulated since enable. */
+WT_API int wt_profile_enable(wt_engine* e, int enable);
+WT_API int wt_profile_read(wt_engine* e, float* ms_out, int32_t* launches_out, int n_stages);
+WT_API int wt_stage_count(void);
+WT_API const char* wt_stage_name(int stage);
+
 /* Thread-local description of the last failure on this thread. */
 WT_API const char* wt_last_error(void);
 WT_API const char* wt_version(void);

@@ -27,6 +27,7 @@ EXPORTED = [
     "wt_engine_create", "wt_engine_destroy", "wt_engine_dims", "wt_set_mel_filters", "wt_set_stream",
     "wt_synchronize", "wt_log_mel", "wt_encode", "wt_decode_greedy", "wt_transcribe_tokens",
     "wt_get_step_logits", "wt_launch_count", "wt_last_error", "wt_version", "wt_debug_gemm_bf16",
+    "wt_profile_enable", "wt_profile_read", "wt_stage_count", "wt_stage_name",
 ]
 
 
@@ -59,6 +60,7 @@ def load_library() -> ctypes.CDLL:
         lib.wt_version.restype = ctypes.c_char_p
         lib.wt_launch_count.restype = ctypes.c_int64
         lib.wt_launch_count.argtypes = [ctypes.c_void_p]
+        lib.wt_stage_name.restype = ctypes.c_char_p
         lib.wt_engine_destroy.restype = None
         lib.wt_engine_destroy.argtypes = [ctypes.c_void_p]
         _lib = lib
@@ -181,6 +183,17 @@ class Engine:
                                              max_total_tokens, ctypes.c_int64(eot), ctypes.c_void_p(i),
                                              ctypes.c_void_p(l), imem))
         return ids_out, lens_out
+
+    def profile(self, enable: bool):
+        _check(self.lib.wt_profile_enable(self.h, int(enable)))
+
+    def profile_read(self):
+        """-> {stage name: (total ms, launches)} accumulated since profile(True)."""
+        n = self.lib.wt_stage_count()
+        ms = (ctypes.c_float * n)()
+        cnt = (ctypes.c_int32 * n)()
+        _check(self.lib.wt_profile_read(self.h, ms, cnt, n))
+        return {self.lib.wt_stage_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n)}
 
     def step_logits(self, step: int, n_clips: int) -> np.ndarray:
         out = np.empty((n_clips, self.dims.n_vocab), dtype=np.float32)

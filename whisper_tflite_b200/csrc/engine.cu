@@ -196,10 +196,37 @@ struct LNp { float* g = nullptr; float* b = nullptr; };
 struct EncLayer { LNp ln1, ln2; Lin qkv, out, fc1, fc2; };
 struct DecLayer { LNp ln1, lnx, ln2; Lin qkv, out, xq, xkv, xout, fc1, fc2; void *kx = nullptr, *vx = nullptr, *kc = nullptr, *vc = nullptr; };
 
+enum Stage {
+  ST_MEL = 0, ST_MEL_LAYOUT, ST_CONV, ST_ENC_LN, ST_ENC_GEMM, ST_ENC_ATTN, ST_XKV, ST_DEC_EMBED, ST_DEC_LN, ST_DEC_GEMM,
+  ST_DEC_SELF_ATTN, ST_DEC_CROSS_ATTN, ST_LOGITS, ST_ARGMAX, ST_COUNT
+};
+const char* kStageNames[ST_COUNT] = {"mel_frames", "mel_layout", "conv_stem", "enc_layernorm", "enc_gemm", "enc_attention",
+                                     "cross_kv", "dec_embed", "dec_layernorm", "dec_gemm", "dec_self_attn",
+                                     "dec_cross_attn", "logits", "argmax"};
+
 }  // namespace
 
 // ================================================================================================
 struct wt_engine {
+  // ---- per-stage CUDA-event profiler (off by default; bench.py's roofline pass turns it on) ----
+  bool profiling = false;
+  bool decoding = false;       // which phase generic ops (linear / layernorm) are attributed to
+  int gemm_stage = -1;         // override for the next linear() (conv stem, cross K/V, logits)
+  int stage = ST_MEL;
+  struct ProfRec { int stage; cudaEvent_t a, b; };
+  std::vector<ProfRec> prof;
+  std::vector<cudaEvent_t> ev_pool;
+  cudaEvent_t get_event() {
+    if (!ev_pool.empty()) { cudaEvent_t e = ev_pool.back(); ev_pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+  }
+  cudaEvent_t pending_a = nullptr;
+  void pre_launch() {
+    if (!profiling) return;
+    pending_a = get_event();
+    cudaEventRecord(pending_a, stream);
+  }
+
   int device = 0;
   int precision = WT_PRECISION_BF16;
   int max_batch = 1;
@@ -287,6 +314,12 @@ struct wt_engine {
   }
   int check_launch(const char* what) {
     ++launches;
+    if (profiling && pending_a) {
+      cudaEvent_t b = get_event();
+      cudaEventRecord(b, stream);
+      prof.push_back({stage, pending_a, b});
+      pending_a = nullptr;
+    }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(WT_ERR_CUDA, "launch of %s failed: %s", what, cudaGetErrorString(e));
     return WT_OK;
@@ -337,6 +370,7 @@ static int launch_gemm_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMap
   p.n_tiles_n = (p.N + BN - 1) / BN;
   const int n_tiles = p.tiles_per_batch * p.n_batches * p.n_tiles_n;
   const int grid = n_tiles < e->num_sms ? n_tiles : e->num_sms;
+  e->pre_launch();
   wt::gemm_bf16_sm100_kernel<BN><<<grid, wt::kGemmThreads, S::kTotal, e->stream>>>(ma, mw, p);
   return e->check_launch("gemm_bf16_sm100_kernel");
 }
@@ -398,6 +432,7 @@ int wt_engine::gemm_bf16(const void* A, const uint64_t* a_dims, const uint64_t* 
 int wt_engine::linear(const void* A, int M, const Lin& L, void* C, int flags, const void* addend,
                       unsigned long long* amax) {
   RowMap plain{0, M, L.N};
+  stage = gemm_stage >= 0 ? gemm_stage : (decoding ? ST_DEC_GEMM : ST_ENC_GEMM);
   if (f32mode()) {
     wt::GemmF32Params p{};
     p.A = (const float*)A;
@@ -415,6 +450,7 @@ int wt_engine::linear(const void* A, int M, const Lin& L, void* C, int flags, co
     p.K = L.K;
     p.flags = (flags & (wt::EPI_GELU)) | (L.b ? wt::EPI_BIAS : 0) | (addend ? wt::EPI_RESIDUAL : 0);
     dim3 grid((L.N + 63) / 64, (M + 63) / 64);
+    pre_launch();
     wt::sgemm_f32_kernel<<<grid, 256, 0, stream>>>(p);
     return check_launch("sgemm_f32_kernel");
   }
@@ -426,7 +462,9 @@ int wt_engine::linear(const void* A, int M, const Lin& L, void* C, int flags, co
 
 int wt_engine::layernorm(const void* in, const LNp& ln, void* out, int rows) {
   const int D = dims.d_model;
+  stage = decoding ? ST_DEC_LN : ST_ENC_LN;
   dim3 grid((rows + 7) / 8);
+  pre_launch();
   if (f32mode())
     wt::layernorm_kernel<float, float><<<grid, 256, 0, stream>>>((const float*)in, ln.g, ln.b, (float*)out, rows, D);
   else
@@ -475,6 +513,8 @@ int wt_engine::log_mel(const float* pcm, int n_clips, int n_samples, int pcm_mem
     src = d_pcm;
   }
   const int n_len = n_samples / wt::kHop;
+  pre_launch();
+  stage = ST_MEL;
   wt::fill_int_kernel<<<(n_clips + 255) / 256, 256, 0, stream>>>(d_clip_max, INT_MIN, n_clips);
   WT_TRY(check_launch("fill_int_kernel"));
   wt::MelParams p{};
@@ -490,11 +530,13 @@ int wt_engine::log_mel(const float* pcm, int n_clips, int n_samples, int pcm_mem
   p.n_len = n_len;
   p.n_mel = n_mel;
   p.n_tiles = (n_len + wt::kTileFrames - 1) / wt::kTileFrames;
+  pre_launch();
   wt::mel_frames_kernel<<<dim3(p.n_tiles, n_clips), wt::kMelThreads, wt::kMelSmemBytes, stream>>>(p);
   WT_TRY(check_launch("mel_frames_kernel"));
   mel_clips = n_clips;
   mel_len = n_len;
   if (finalize) {
+    pre_launch();
     wt::mel_finalize_f32_kernel<<<num_sms * 4, 256, 0, stream>>>(d_mel_raw, d_clip_max, d_mel, n_mel * n_len, n_clips);
     WT_TRY(check_launch("mel_finalize_f32_kernel"));
     if (out)
@@ -671,6 +713,9 @@ int wt_engine::encode(const float* mel, int n_clips, int mel_mem, float* states_
   // [B][80][3000] f32 -> zero-padded time-major [B][3002][80] (clamp + affine fused when reading raw)
   {
     dim3 grid((T + 31) / 32, (nm + 31) / 32, n_clips);
+    stage = ST_MEL_LAYOUT;
+    decoding = false;
+    pre_launch();
     if (f32mode())
       wt::mel_to_time_major_kernel<float><<<grid, 256, 0, stream>>>(src, cmax, (float*)mel_tm, nm, T);
     else
@@ -678,6 +723,7 @@ int wt_engine::encode(const float* mel, int n_clips, int mel_mem, float* states_
     WT_TRY(check_launch("mel_to_time_major_kernel"));
   }
   const int M1 = n_clips * T, M2 = n_clips * S;
+  stage = ST_CONV;
   if (f32mode()) {
     wt::GemmF32Params p{};
     // conv1 + GELU -> interior rows of x1
@@ -693,6 +739,7 @@ int wt_engine::encode(const float* mel, int n_clips, int mel_mem, float* states_
     p.N = d;
     p.K = 3 * nm;
     p.flags = wt::EPI_BIAS | wt::EPI_GELU;
+    pre_launch();
     wt::sgemm_f32_kernel<<<dim3((d + 63) / 64, (M1 + 63) / 64), 256, 0, stream>>>(p);
     WT_TRY(check_launch("sgemm_f32_kernel(conv1)"));
     // conv2 (stride 2) + GELU + positional rows -> x
@@ -710,6 +757,7 @@ int wt_engine::encode(const float* mel, int n_clips, int mel_mem, float* states_
     q.N = d;
     q.K = 3 * d;
     q.flags = wt::EPI_BIAS | wt::EPI_GELU | wt::EPI_POS;
+    pre_launch();
     wt::sgemm_f32_kernel<<<dim3((d + 63) / 64, (M2 + 63) / 64), 256, 0, stream>>>(q);
     WT_TRY(check_launch("sgemm_f32_kernel(conv2)"));
   } else {
@@ -729,14 +777,18 @@ int wt_engine::encode(const float* mel, int n_clips, int mel_mem, float* states_
                        wt::EPI_GELU | wt::EPI_ADD, enc_pos, RowMap{0, S, d}, nullptr));
     }
   }
+  gemm_stage = -1;
   for (int l = 0; l < dims.n_enc_layers; ++l) {
     EncLayer& L = enc[l];
     WT_TRY(layernorm(x, L.ln1, xn, M2));
     WT_TRY(linear(xn, M2, L.qkv, qkv, 0));
+    stage = ST_ENC_ATTN;
     if (f32mode()) {
+      pre_launch();
       wt::attention_simt_kernel<float><<<dim3((S + 127) / 128, H, n_clips), 128, 0, stream>>>((const float*)qkv, (float*)att, S, H);
       WT_TRY(check_launch("attention_simt_kernel"));
     } else {
+      pre_launch();
       wt::attention_simt_kernel<bf16><<<dim3((S + 127) / 128, H, n_clips), 128, 0, stream>>>((const bf16*)qkv, (bf16*)att, S, H);
       WT_TRY(check_launch("attention_simt_kernel"));
     }
@@ -750,7 +802,11 @@ int wt_engine::encode(const float* mel, int n_clips, int mel_mem, float* states_
   // decoder Invoke: whisper.cpp:375)
   for (int l = 0; l < dims.n_dec_layers; ++l) {
     DecLayer& L = dec[l];
+    gemm_stage = ST_XKV;
     WT_TRY(linear(enc_out, M2, L.xkv, qkv, 0));
+    gemm_stage = -1;
+    stage = ST_XKV;
+    pre_launch();
     if (f32mode())
       wt::split_heads_kv_kernel<float><<<num_sms * 4, 256, 0, stream>>>((const float*)qkv, (float*)L.kx, (float*)L.vx, n_clips, S, H);
     else
@@ -769,6 +825,7 @@ int wt_engine::encode(const float* mel, int n_clips, int mel_mem, float* states_
         if (!io_f32) WT_TRY(alloc(&io_f32, (size_t)max_batch * S * d));
         tmp = io_f32;
       }
+      pre_launch();
       wt::convert_kernel<bf16, float><<<num_sms * 4, 256, 0, stream>>>((const bf16*)enc_out, tmp, (long long)n);
       WT_TRY(check_launch("convert_kernel"));
       if (out_mem == WT_HOST) WT_CUDA_OK(cudaMemcpyAsync(dst, tmp, n * 4, cudaMemcpyDeviceToHost, stream));
@@ -782,6 +839,8 @@ template <class T>
 static int decode_step_attn(wt_engine* e, DecLayer& L, int n_clips, int pos, bool cross) {
   const int H = e->dims.n_heads, S = e->dims.n_audio_ctx;
   if (!cross) {
+    e->stage = ST_DEC_SELF_ATTN;
+    e->pre_launch();
     wt::decode_self_attn_kernel<T><<<dim3(H, n_clips), 64, 0, e->stream>>>((const T*)e->dqkv, (T*)L.kc, (T*)L.vc, (T*)e->datt, pos, 32, H);
     return e->check_launch("decode_self_attn_kernel");
   }
@@ -789,6 +848,8 @@ static int decode_step_attn(wt_engine* e, DecLayer& L, int n_clips, int pos, boo
   int nsplit = (2 * e->num_sms + n_clips * H - 1) / (n_clips * H);
   if (nsplit < 1) nsplit = 1;
   if (nsplit > wt::kXaMaxSplit) nsplit = wt::kXaMaxSplit;
+  e->stage = ST_DEC_CROSS_ATTN;
+  e->pre_launch();
   wt::decode_cross_attn_kernel<T><<<dim3(nsplit, H, n_clips), 128, 0, e->stream>>>((const T*)e->dq, (const T*)L.kx, (const T*)L.vx, (T*)e->datt,
                                                                                    e->xa_part, e->xa_tickets, S, H);
   return e->check_launch("decode_cross_attn_kernel");
@@ -810,6 +871,10 @@ int wt_engine::decode(int n_clips, const int64_t* prompt, int prompt_len, int ma
     hp[i] = (int)prompt[i];
   }
   WT_CUDA_OK(cudaMemcpyAsync(d_prompt, hp, prompt_len * 4, cudaMemcpyHostToDevice, stream));
+  decoding = true;
+  gemm_stage = -1;
+  stage = ST_DEC_EMBED;
+  pre_launch();
   wt::init_decode_state_kernel<<<n_clips, 32, 0, stream>>>(d_prompt, prompt_len, tokens, 32, lens, done);
   WT_TRY(check_launch("init_decode_state_kernel"));
   Lin logit_lin;
@@ -820,6 +885,8 @@ int wt_engine::decode(int n_clips, const int64_t* prompt, int prompt_len, int ma
   // position `pos` = index of the last token fed; the reference feeds i+1 tokens for i = prompt_len-1 .. 29 and
   // appends one (whisper.cpp:367-395), so positions 0 .. max_total-2 are consumed and logits start at prompt_len-1.
   for (int pos = 0; pos <= max_total - 2; ++pos) {
+    stage = ST_DEC_EMBED;
+    pre_launch();
     if (f32mode())
       wt::embed_kernel<float><<<n_clips, 128, 0, stream>>>(tokens, 32, pos, (const float*)tok_emb, (const float*)dec_pos, (float*)dx, d);
     else
@@ -842,6 +909,8 @@ int wt_engine::decode(int n_clips, const int64_t* prompt, int prompt_len, int ma
     if (pos < prompt_len - 1) continue;
     WT_TRY(layernorm(dx, dec_ln, dxn, n_clips));
     const int step = pos - (prompt_len - 1);
+    gemm_stage = ST_LOGITS;
+    stage = ST_LOGITS;
     if (f32mode() || keep_logits) {
       float* lg = keep_logits ? step_logits + (size_t)step * max_batch * V : logits;
       if (f32mode()) {
@@ -852,6 +921,9 @@ int wt_engine::decode(int n_clips, const int64_t* prompt, int prompt_len, int ma
         WT_TRY(gemm_bf16(dxn, ad, as, n_clips, 1, logit_lin, d, 1, 0, nullptr, nullptr, lg, RowMap{0, n_clips, V},
                          wt::EPI_OUT_F32, nullptr, RowMap{0, 1, 0}, nullptr));
       }
+      gemm_stage = -1;
+      stage = ST_ARGMAX;
+      pre_launch();
       wt::argmax_append_kernel<<<n_clips, 256, 0, stream>>>(lg, V, tokens, 32, lens, done, pos, (int)eot);
       WT_TRY(check_launch("argmax_append_kernel"));
     } else {
@@ -861,10 +933,14 @@ int wt_engine::decode(int n_clips, const int64_t* prompt, int prompt_len, int ma
       const uint64_t as[2] = {(uint64_t)d * 2, (uint64_t)d * 2 * n_clips};
       WT_TRY(gemm_bf16(dxn, ad, as, n_clips, 1, logit_lin, d, 1, 0, nullptr, nullptr, nullptr, RowMap{0, n_clips, V},
                        wt::EPI_ARGMAX, nullptr, RowMap{0, 1, 0}, argmax_part, bn));
+      gemm_stage = -1;
+      stage = ST_ARGMAX;
+      pre_launch();
       wt::argmax_partials_kernel<<<n_clips, 128, 0, stream>>>(argmax_part, n_part, tokens, 32, lens, done, pos, (int)eot);
       WT_TRY(check_launch("argmax_partials_kernel"));
     }
   }
+  decoding = false;
   // results: [n_clips][max_total] ids (tokens has stride 32), lens
   if (out_mem == WT_HOST) {
     std::vector<int> ht((size_t)n_clips * 32), hl(n_clips);
@@ -994,6 +1070,33 @@ int wt_get_step_logits(wt_engine* e, int step, int n_clips, float* out, int out_
 }
 
 int64_t wt_launch_count(const wt_engine* e) { return e ? e->launches : 0; }
+
+int wt_profile_enable(wt_engine* e, int enable) {
+  if (!e) return fail(WT_ERR_INVALID, "engine is null");
+  cudaSetDevice(e->device);
+  WT_CUDA_OK(cudaStreamSynchronize(e->stream));
+  for (auto& r : e->prof) { e->ev_pool.push_back(r.a); e->ev_pool.push_back(r.b); }
+  e->prof.clear();
+  e->profiling = enable != 0;
+  return WT_OK;
+}
+
+int wt_profile_read(wt_engine* e, float* ms_out, int32_t* launches_out, int n_stages) {
+  if (!e || !ms_out || !launches_out || n_stages < ST_COUNT) return fail(WT_ERR_INVALID, "need arrays of >= %d stages", (int)ST_COUNT);
+  cudaSetDevice(e->device);
+  WT_CUDA_OK(cudaStreamSynchronize(e->stream));
+  for (int i = 0; i < n_stages; ++i) { ms_out[i] = 0.0f; launches_out[i] = 0; }
+  for (auto& r : e->prof) {
+    float ms = 0.0f;
+    WT_CUDA_OK(cudaEventElapsedTime(&ms, r.a, r.b));
+    ms_out[r.stage] += ms;
+    launches_out[r.stage] += 1;
+  }
+  return WT_OK;
+}
+
+int wt_stage_count(void) { return ST_COUNT; }
+const char* wt_stage_name(int i) { return (i >= 0 && i < ST_COUNT) ? kStageNames[i] : ""; }
 
 int wt_debug_gemm_bf16(void* cuda_stream, const void* A, const void* W, const float* bias, void* C, int M, int N, int K,
                        int flags) {
