@@ -146,7 +146,7 @@ class Engine:
         p, mem, _k = _ptr_mem(mel)
         if mel is not None:
             n_clips = mel.shape[0]
-        if out is None and want_states:
+        if out is None and want_states and self.dims is not None:
             out = np.empty((n_clips, self.dims.n_audio_ctx, self.dims.d_model), dtype=np.float32)
         o, omem, _k2 = _ptr_mem(out)
         _check(self.lib.wt_encode(self.h, ctypes.c_void_p(p) if p else None, n_clips, mem,
