@@ -22,6 +22,7 @@
 #include <vector>
 
 #include "../../include/whisper_b200.h"
+#include "attn_sm100.cuh"
 #include "gemm_sm100.cuh"
 #include "mel_host.h"
 #include "mel_kernels.cuh"
@@ -788,9 +789,19 @@ int wt_engine::encode(const float* mel, int n_clips, int mel_mem, float* states_
       wt::attention_simt_kernel<float><<<dim3((S + 127) / 128, H, n_clips), 128, 0, stream>>>((const float*)qkv, (float*)att, S, H);
       WT_TRY(check_launch("attention_simt_kernel"));
     } else {
+      CUtensorMap mq;
+      const uint64_t qd[3] = {(uint64_t)3 * d, (uint64_t)S, (uint64_t)n_clips};
+      const uint64_t qs[2] = {(uint64_t)3 * d * 2, (uint64_t)S * 3 * d * 2};
+      const uint32_t qbox[3] = {64, 128, 1};
+      WT_TRY(get_map(&mq, qkv, 3, qd, qs, qbox));
+      static bool attn_attr[64] = {};
+      if (!attn_attr[device & 63]) {
+        WT_CUDA_OK(cudaFuncSetAttribute(wt::attention_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::AttnSmem::kTotal));
+        attn_attr[device & 63] = true;
+      }
       pre_launch();
-      wt::attention_simt_kernel<bf16><<<dim3((S + 127) / 128, H, n_clips), 128, 0, stream>>>((const bf16*)qkv, (bf16*)att, S, H);
-      WT_TRY(check_launch("attention_simt_kernel"));
+      wt::attention_sm100_kernel<<<dim3((S + 127) / 128, H, n_clips), wt::kAtThreads, wt::AttnSmem::kTotal, stream>>>(mq, (bf16*)att, S, H);
+      WT_TRY(check_launch("attention_sm100_kernel"));
     }
     WT_TRY(linear(att, M2, L.out, x, 0, x));
     WT_TRY(layernorm(x, L.ln2, xn, M2));
@@ -844,8 +855,8 @@ static int decode_step_attn(wt_engine* e, DecLayer& L, int n_clips, int pos, boo
     wt::decode_self_attn_kernel<T><<<dim3(H, n_clips), 64, 0, e->stream>>>((const T*)e->dqkv, (T*)L.kc, (T*)L.vc, (T*)e->datt, pos, 32, H);
     return e->check_launch("decode_self_attn_kernel");
   }
-  // enough splits to put >= 2 CTAs on every SM
-  int nsplit = (2 * e->num_sms + n_clips * H - 1) / (n_clips * H);
+  // enough splits to keep >= 8 streaming CTAs on every SM
+  int nsplit = (8 * e->num_sms + n_clips * H - 1) / (n_clips * H);
   if (nsplit < 1) nsplit = 1;
   if (nsplit > wt::kXaMaxSplit) nsplit = wt::kXaMaxSplit;
   e->stage = ST_DEC_CROSS_ATTN;

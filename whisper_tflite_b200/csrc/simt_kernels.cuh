@@ -283,56 +283,132 @@ __global__ void __launch_bounds__(64) decode_self_attn_kernel(const T* qkv, T* k
 }
 
 // Cross-attention for one decode step: q [B][D] against the per-clip encoder K/V
-// ([B][H][S][64], written once per clip by the cross-K/V projection). The S keys are split over
-// `nsplit` blocks per (clip, head); each block streams its slice once (this is the HBM-bound part
-// of a decode step), keeps a local (max, sum, acc[64]) and writes a partial; the last block to
+// ([B][H][S][64], written once per clip by the cross-K/V projection). This is the HBM-bound part of a
+// decode step (every step re-reads all K/V: 2*S*D elements per clip per layer), so the kernel is a pure
+// stream: the S keys are split over `nsplit` blocks per (clip, head); 8 lanes share a key (one 16-byte
+// load each, 4 keys = 512 contiguous bytes per warp instruction, 4 such loads in flight per lane);
+// pass 1 parks the scores in shared memory, a block max/sum gives the softmax weights with no per-key
+// rescaling chain, pass 2 streams V. Each block writes a partial (acc[64], max, sum); the last block to
 // finish (atomic ticket) merges the partials. grid = (nsplit, H, B), block = 128 (4 warps).
 constexpr int kXaMaxSplit = 16;
+constexpr int kXaMaxKeys = 1536;
+
+template <class T> __device__ __forceinline__ void load8(const T* p, float* f);
+template <> __device__ __forceinline__ void load8<float>(const float* p, float* f) {
+  const float4 a = *reinterpret_cast<const float4*>(p);
+  const float4 b = *reinterpret_cast<const float4*>(p + 4);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+template <> __device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float* f) {
+  const uint4 v = *reinterpret_cast<const uint4*>(p);
+  const unsigned w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    f[2 * j] = __uint_as_float(w[j] << 16);
+    f[2 * j + 1] = __uint_as_float(w[j] & 0xffff0000u);
+  }
+}
+
 template <class T>
 __global__ void __launch_bounds__(128) decode_cross_attn_kernel(const T* q, const T* kx, const T* vx, T* out,
                                                                  float* part, unsigned* tickets, int S, int H) {
-  __shared__ float sq[64];
-  __shared__ float s_m[4], s_l[4], s_o[4][64];
+  __shared__ float s_sc[kXaMaxKeys];
+  __shared__ float s_red[4];
+  __shared__ float s_o[4][64];
   __shared__ unsigned s_last;
   const int sp = blockIdx.x, nsplit = gridDim.x, h = blockIdx.y, b = blockIdx.z, D = H * 64;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  if (tid < 64) sq[tid] = to_f32<T>(q[(long long)b * D + h * 64 + tid]) * 0.125f;
-  __syncthreads();
-  const int per = (S + nsplit - 1) / nsplit;
-  const int k_begin = sp * per, k_end = (k_begin + per < S) ? (k_begin + per) : S;
+  const int grp = lane >> 3, sub = lane & 7;  // 4 keys per warp instruction, 8 lanes (x 8 dims) per key
+  int per = (S + nsplit - 1) / nsplit;
+  per = (per + 15) & ~15;
+  const int k_begin = sp * per;
+  const int k_end = (k_begin + per < S) ? (k_begin + per) : S;
+  const int nk = k_end > k_begin ? k_end - k_begin : 0;
   const T* kb = kx + ((long long)(b * H + h) * S) * 64;
   const T* vb = vx + ((long long)(b * H + h) * S) * 64;
-  // each lane owns dims (2*lane, 2*lane+1); a warp handles one key at a time
-  const float q0 = sq[2 * lane], q1 = sq[2 * lane + 1];
-  float m = -3.0e38f, l = 0.0f, o0 = 0.0f, o1 = 0.0f;
-  for (int key = k_begin + warp; key < k_end; key += 4) {
-    const T* kr = kb + (long long)key * 64 + 2 * lane;
-    const T* vr = vb + (long long)key * 64 + 2 * lane;
-    float s = warp_sum(q0 * to_f32<T>(kr[0]) + q1 * to_f32<T>(kr[1]));
-    const float mn = fmaxf(m, s);
-    const float sc = __expf(m - mn), pw = __expf(s - mn);
-    l = l * sc + pw;
-    o0 = o0 * sc + pw * to_f32<T>(vr[0]);
-    o1 = o1 * sc + pw * to_f32<T>(vr[1]);
-    m = mn;
+  float qv[8];
+  load8<T>(q + (long long)b * D + h * 64 + sub * 8, qv);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) qv[i] *= 0.125f;
+
+  // ---- pass 1: scores -> shared ----
+  for (int kw = warp * 4; kw < nk; kw += 64) {  // warp-uniform trip count (shuffles below)
+    const int k0 = kw + grp;                      // 4 keys in flight per lane: k0, k0+16, k0+32, k0+48
+    float kf[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int kk = k0 + 16 * u;
+      if (kk < nk) load8<T>(kb + (long long)(k_begin + kk) * 64 + sub * 8, kf[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int kk = k0 + 16 * u;
+      float s = 0.0f;
+      if (kk < nk) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s = fmaf(qv[i], kf[u][i], s);
+      }
+      s += __shfl_xor_sync(0xffffffffu, s, 1);
+      s += __shfl_xor_sync(0xffffffffu, s, 2);
+      s += __shfl_xor_sync(0xffffffffu, s, 4);
+      if (sub == 0 && kk < nk) s_sc[kk] = s;
+    }
   }
-  if (lane == 0) { s_m[warp] = m; s_l[warp] = l; }
-  s_o[warp][2 * lane] = o0;
-  s_o[warp][2 * lane + 1] = o1;
   __syncthreads();
-  // merge the 4 warps -> partial for this split
+  // ---- block max, weights, sum ----
+  float m = -3.0e38f;
+  for (int i = tid; i < nk; i += 128) m = fmaxf(m, s_sc[i]);
+  m = warp_max(m);
+  if (lane == 0) s_red[warp] = m;
+  __syncthreads();
+  m = fmaxf(fmaxf(s_red[0], s_red[1]), fmaxf(s_red[2], s_red[3]));
+  __syncthreads();
+  float l = 0.0f;
+  for (int i = tid; i < nk; i += 128) {
+    const float pw = __expf(s_sc[i] - m);
+    s_sc[i] = pw;
+    l += pw;
+  }
+  l = warp_sum(l);
+  if (lane == 0) s_red[warp] = l;
+  __syncthreads();
+  l = s_red[0] + s_red[1] + s_red[2] + s_red[3];
+  // ---- pass 2: acc[dims] += p * V ----
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.0f;
+  for (int kw = warp * 4; kw < nk; kw += 64) {
+    const int k0 = kw + grp;
+    float vf[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int kk = k0 + 16 * u;
+      if (kk < nk) load8<T>(vb + (long long)(k_begin + kk) * 64 + sub * 8, vf[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int kk = k0 + 16 * u;
+      if (kk < nk) {
+        const float pw = s_sc[kk];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = fmaf(pw, vf[u][i], acc[i]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 8);
+    acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 16);
+  }
+  if (grp == 0) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s_o[warp][sub * 8 + i] = acc[i];
+  }
+  __syncthreads();
   float* pp = part + (((long long)(b * H + h) * kXaMaxSplit) + sp) * 66;
   if (tid < 64) {
-    float M = fmaxf(fmaxf(s_m[0], s_m[1]), fmaxf(s_m[2], s_m[3]));
-    float L = 0.0f, O = 0.0f;
-#pragma unroll
-    for (int w = 0; w < 4; ++w) {
-      const float sc = __expf(s_m[w] - M);
-      L += s_l[w] * sc;
-      O += s_o[w][tid] * sc;
-    }
-    pp[tid] = O;
-    if (tid == 0) { pp[64] = M; pp[65] = L; }
+    pp[tid] = s_o[0][tid] + s_o[1][tid] + s_o[2][tid] + s_o[3][tid];
+    if (tid == 0) { pp[64] = m; pp[65] = l; }
   }
 #ifndef WT_CUDA_EMU
   __threadfence();
