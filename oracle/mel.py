@@ -148,3 +148,19 @@ def ref_wav_read_legacy(path: str, cap: int = 1 << 24) -> np.ndarray:
     out = np.zeros(cap, dtype=np.float32)
     n = _lib(REF_SO).ref_wav_read_legacy(path.encode(), _ptr(out), cap)
     return out[:min(n, cap)].copy()
+
+
+def ref_wav_read(path: str, cap: int = 1 << 24) -> np.ndarray:
+    out = np.zeros(cap, dtype=np.float32)
+    n = _lib(REF_SO).ref_wav_read(path.encode(), _ptr(out), cap)
+    return out[:min(n, cap)].copy()
+
+
+def ref_lang_code(i: int) -> str:
+    lib = _lib(REF_SO)
+    lib.ref_lang_code.restype = ctypes.c_char_p
+    return lib.ref_lang_code(int(i)).decode()
+
+
+def ref_language_count() -> int:
+    return int(_lib(REF_SO).ref_language_count())

@@ -99,5 +99,16 @@ int ref_wav_read_legacy(const char* path, float* out, int cap) {
   return n;
 }
 
+// wav_util.cpp:89-129 (dr_wav based)
+int ref_wav_read(const char* path, float* out, int cap) {
+  std::vector<float> v = whisper::wav_read(path);
+  int n = static_cast<int>(v.size());
+  if (out) std::memcpy(out, v.data(), sizeof(float) * (n < cap ? n : cap));
+  return n;
+}
+
+const char* ref_lang_code(int id) { return whisper::lang_code(static_cast<size_t>(id)).c_str(); }
+int ref_language_count() { return static_cast<int>(whisper::language_meta.size()); }
+
 int ref_hardware_concurrency() { return static_cast<int>(std::thread::hardware_concurrency()); }
 }

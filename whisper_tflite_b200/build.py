@@ -48,12 +48,20 @@ def build_cuda(force: bool = False, verbose: bool = False) -> str:
 def build_host(force: bool = False) -> str:
     if not os.path.isdir(HOST):
         return ""
-    srcs = [os.path.join(HOST, f) for f in sorted(os.listdir(HOST)) if f.endswith(".cpp") and not f.startswith("app_")]
+    srcs = [os.path.join(HOST, f) for f in sorted(os.listdir(HOST)) if f.endswith(".cpp") and not f.startswith(("app_", "jni_"))]
     deps = srcs + [os.path.join(HOST, f) for f in os.listdir(HOST) if f.endswith(".h")] + [LIB]
     if srcs and (force or _newer(HOST_LIB, deps)):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", HOST_LIB] + srcs +
                               ["-I", os.path.join(os.path.dirname(HERE), "include"), "-L", CSRC, "-lwhisper_b200",
                                "-Wl,-rpath,$ORIGIN/..", "-lpthread"])
+    # the JNI bridge has no JDK to link against here: compile-check it against the declaration-only stub
+    jni = os.path.join(HOST, "jni_whisper.cpp")
+    jni_o = os.path.join(HOST, "jni_whisper.o")
+    if os.path.exists(jni) and (force or _newer(jni_o, [jni, os.path.join(HOST, "whisper.h")])):
+        jdk = os.environ.get("JAVA_HOME")
+        inc = (["-I", os.path.join(jdk, "include"), "-I", os.path.join(jdk, "include", "linux")] if jdk and
+               os.path.exists(os.path.join(jdk, "include", "jni.h")) else ["-I", os.path.join(HOST, "jni_stub")])
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-c", jni, "-o", jni_o, "-I", HOST] + inc)
     for app in ("encdec", "minimal"):
         src = os.path.join(HOST, f"app_{app}.cpp")
         exe = os.path.join(HOST, app)
