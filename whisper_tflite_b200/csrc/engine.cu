@@ -23,6 +23,7 @@
 
 #include "../../include/whisper_b200.h"
 #include "attn_sm100.cuh"
+#include "decoder_sm100.cuh"
 #include "gemm_sm100.cuh"
 #include "mel_host.h"
 #include "mel_kernels.cuh"
@@ -199,11 +200,11 @@ struct DecLayer { LNp ln1, lnx, ln2; Lin qkv, out, xq, xkv, xout, fc1, fc2; void
 
 enum Stage {
   ST_MEL = 0, ST_MEL_LAYOUT, ST_CONV, ST_ENC_LN, ST_ENC_GEMM, ST_ENC_ATTN, ST_XKV, ST_DEC_EMBED, ST_DEC_LN, ST_DEC_GEMM,
-  ST_DEC_SELF_ATTN, ST_DEC_CROSS_ATTN, ST_LOGITS, ST_ARGMAX, ST_COUNT
+  ST_DEC_SELF_ATTN, ST_DEC_CROSS_ATTN, ST_LOGITS, ST_ARGMAX, ST_DEC_PERSISTENT, ST_COUNT
 };
 const char* kStageNames[ST_COUNT] = {"mel_frames", "mel_layout", "conv_stem", "enc_layernorm", "enc_gemm", "enc_attention",
                                      "cross_kv", "dec_embed", "dec_layernorm", "dec_gemm", "dec_self_attn",
-                                     "dec_cross_attn", "logits", "argmax"};
+                                     "dec_cross_attn", "logits", "argmax", "dec_persistent"};
 
 }  // namespace
 
@@ -265,6 +266,16 @@ struct wt_engine {
   unsigned* xa_tickets = nullptr;
   unsigned long long* argmax_part = nullptr;
   int *tokens = nullptr, *lens = nullptr, *done = nullptr, *d_prompt = nullptr;
+  // persistent decoder (bf16, d_model <= 768): one cooperative launch per group of <= 64 clips
+  bool dec_persistent = false;
+  int dec_grid = 0;
+  wt::DecLayerDev* d_dec_layers = nullptr;
+  float *pd_x = nullptr, *pd_qs = nullptr, *pd_att = nullptr, *pd_qx = nullptr, *pd_xpart = nullptr;
+  bf16* pd_hmid = nullptr;
+  unsigned *pd_xtickets = nullptr, *pd_bar = nullptr;
+  unsigned long long* pd_amax = nullptr;
+  int* pd_status = nullptr;
+  int pd_xslots_cap = 0;
   int enc_clips = 0;  // clips whose encoder states / cross K,V are resident
   std::map<std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint64_t, uint64_t, uint32_t>, CUtensorMap> map_cache;
 
@@ -334,6 +345,9 @@ struct wt_engine {
   int encode(const float* mel, int n_clips, int mel_mem, float* states_out, int out_mem, bool from_raw);
   int decode(int n_clips, const int64_t* prompt, int prompt_len, int max_total, int64_t eot, int32_t* ids, int32_t* lens_o,
              int out_mem);
+  int copy_decode_results(int n_clips, int max_total, int32_t* ids, int32_t* lens_o, int out_mem);
+  int init_persistent_decoder();
+  int decode_persistent(int n_clips, int prompt_len, int max_total, int eot);
 
   // ---- op wrappers ----
   int gemm_bf16(const void* A, const uint64_t* a_dims, const uint64_t* a_strides, int rows_per_batch, int n_batches,
@@ -689,6 +703,91 @@ int wt_engine::load_model(const char* path) {
   WT_TRY(alloc(&done, B));
   WT_TRY(alloc(&d_prompt, 32));
   has_model = true;
+  return init_persistent_decoder();
+}
+
+// The persistent decoder needs every CTA co-resident (grid barriers): cooperative launch, one CTA per SM.
+int wt_engine::init_persistent_decoder() {
+  const char* ov = getenv("WT_DECODER");
+  if (f32mode() || dims.d_model > wt::kDecMaxD || (ov && strcmp(ov, "legacy") == 0)) return WT_OK;
+  int coop = 0;
+  WT_CUDA_OK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device));
+  if (!coop) return WT_OK;
+  WT_CUDA_OK(cudaFuncSetAttribute(wt::decoder_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::DecSmem::kTotal));
+  int per_sm = 0;
+  WT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wt::decoder_persistent_kernel, wt::kDecThreads, wt::DecSmem::kTotal));
+  if (per_sm < 1) return fail(WT_ERR_CUDA, "decoder_persistent_kernel does not fit one CTA per SM");
+  dec_grid = num_sms;
+  const int d = dims.d_model, H = dims.n_heads, S = dims.n_audio_ctx;
+  std::vector<wt::DecLayerDev> hl(dims.n_dec_layers);
+  for (int i = 0; i < dims.n_dec_layers; ++i) {
+    DecLayer& L = dec[i];
+    wt::DecLayerDev& o = hl[i];
+    o.ln1_g = L.ln1.g; o.ln1_b = L.ln1.b; o.lnx_g = L.lnx.g; o.lnx_b = L.lnx.b; o.ln2_g = L.ln2.g; o.ln2_b = L.ln2.b;
+    o.w_qkv = (const bf16*)L.qkv.w; o.b_qkv = L.qkv.b;
+    o.w_out = (const bf16*)L.out.w; o.b_out = L.out.b;
+    o.w_xq = (const bf16*)L.xq.w; o.b_xq = L.xq.b;
+    o.w_xout = (const bf16*)L.xout.w; o.b_xout = L.xout.b;
+    o.w_fc1 = (const bf16*)L.fc1.w; o.b_fc1 = L.fc1.b;
+    o.w_fc2 = (const bf16*)L.fc2.w; o.b_fc2 = L.fc2.b;
+    o.kx = (const bf16*)L.kx; o.vx = (const bf16*)L.vx;
+    o.kc = (bf16*)L.kc; o.vc = (bf16*)L.vc;
+  }
+  WT_TRY(alloc(&d_dec_layers, hl.size()));
+  WT_CUDA_OK(cudaMemcpy(d_dec_layers, hl.data(), hl.size() * sizeof(wt::DecLayerDev), cudaMemcpyHostToDevice));
+  const size_t R = wt::kDecMaxClips;
+  WT_TRY(alloc(&pd_x, R * d));
+  WT_TRY(alloc(&pd_qs, R * d));
+  WT_TRY(alloc(&pd_att, R * d));
+  WT_TRY(alloc(&pd_qx, R * d));
+  WT_TRY(alloc(&pd_hmid, R * 4 * d));
+  // worst case slots per (clip, head): one clip in flight -> per = ceil(H*S/grid) keys per CTA
+  const long long per_min = ((long long)H * S + dec_grid - 1) / dec_grid;
+  pd_xslots_cap = (int)((S + per_min - 1) / per_min) + 1;
+  WT_TRY(alloc(&pd_xpart, R * H * (size_t)pd_xslots_cap * 66));
+  WT_TRY(alloc(&pd_xtickets, R * H, true));
+  WT_TRY(alloc(&pd_amax, R * (size_t)dec_grid));
+  WT_TRY(alloc(&pd_bar, 4, true));
+  WT_TRY(alloc(&pd_status, 4, true));
+  dec_persistent = true;
+  return WT_OK;
+}
+
+int wt_engine::decode_persistent(int n_clips, int prompt_len, int max_total, int eot) {
+  const int d = dims.d_model, H = dims.n_heads, S = dims.n_audio_ctx;
+  for (int c0 = 0; c0 < n_clips; c0 += wt::kDecMaxClips) {
+    const int nb = (n_clips - c0 < wt::kDecMaxClips) ? n_clips - c0 : wt::kDecMaxClips;
+    WT_CUDA_OK(cudaMemsetAsync(pd_bar, 0, 4 * sizeof(unsigned), stream));
+    WT_CUDA_OK(cudaMemsetAsync(pd_status, 0, 4 * sizeof(int), stream));
+    WT_CUDA_OK(cudaMemsetAsync(pd_xtickets, 0, (size_t)wt::kDecMaxClips * H * sizeof(unsigned), stream));
+    wt::DecParams p{};
+    p.layers = d_dec_layers;
+    p.n_layers = dims.n_dec_layers;
+    p.n_clips = nb;
+    p.clip0 = c0;
+    p.d = d; p.H = H; p.S = S; p.V = dims.n_vocab;
+    p.tok_emb = (const bf16*)tok_emb;
+    p.pos_emb = (const bf16*)dec_pos;
+    p.lnf_g = dec_ln.g; p.lnf_b = dec_ln.b;
+    p.tokens = tokens; p.lens = lens; p.done = done;
+    p.prompt_len = prompt_len; p.max_total = max_total; p.eot = eot;
+    p.x = pd_x; p.qs = pd_qs; p.att = pd_att; p.qx = pd_qx; p.hmid = pd_hmid;
+    p.xpart = pd_xpart; p.xtickets = pd_xtickets;
+    const long long per = ((long long)nb * H * S + dec_grid - 1) / dec_grid;
+    p.xslots = (int)((S + per - 1) / per) + 1;
+    if (p.xslots > pd_xslots_cap) return fail(WT_ERR_STATE, "cross-attention partial slots %d exceed capacity %d", p.xslots, pd_xslots_cap);
+    p.amax_part = pd_amax;
+    p.step_logits = keep_logits ? step_logits : nullptr;
+    p.step_logits_stride = (long long)max_batch * dims.n_vocab;
+    p.bar = pd_bar;
+    p.status = pd_status;
+    void* args[] = {&p};
+    stage = ST_DEC_PERSISTENT;
+    pre_launch();
+    WT_CUDA_OK(cudaLaunchCooperativeKernel((void*)wt::decoder_persistent_kernel, dim3(dec_grid), dim3(wt::kDecThreads), args,
+                                           (size_t)wt::DecSmem::kTotal, stream));
+    WT_TRY(check_launch("decoder_persistent_kernel"));
+  }
   return WT_OK;
 }
 
@@ -888,6 +987,11 @@ int wt_engine::decode(int n_clips, const int64_t* prompt, int prompt_len, int ma
   pre_launch();
   wt::init_decode_state_kernel<<<n_clips, 32, 0, stream>>>(d_prompt, prompt_len, tokens, 32, lens, done);
   WT_TRY(check_launch("init_decode_state_kernel"));
+  if (dec_persistent) {
+    WT_TRY(decode_persistent(n_clips, prompt_len, max_total, (int)eot));
+    decoding = false;
+    return copy_decode_results(n_clips, max_total, ids, lens_o, out_mem);
+  }
   Lin logit_lin;
   logit_lin.w = tok_emb;
   logit_lin.b = nullptr;
@@ -952,12 +1056,19 @@ int wt_engine::decode(int n_clips, const int64_t* prompt, int prompt_len, int ma
     }
   }
   decoding = false;
-  // results: [n_clips][max_total] ids (tokens has stride 32), lens
+  return copy_decode_results(n_clips, max_total, ids, lens_o, out_mem);
+}
+
+// results: [n_clips][max_total] ids (tokens has stride 32), lens
+int wt_engine::copy_decode_results(int n_clips, int max_total, int32_t* ids, int32_t* lens_o, int out_mem) {
   if (out_mem == WT_HOST) {
     std::vector<int> ht((size_t)n_clips * 32), hl(n_clips);
     WT_CUDA_OK(cudaMemcpyAsync(ht.data(), tokens, ht.size() * 4, cudaMemcpyDeviceToHost, stream));
     WT_CUDA_OK(cudaMemcpyAsync(hl.data(), lens, hl.size() * 4, cudaMemcpyDeviceToHost, stream));
+    int st[4] = {0, 0, 0, 0};
+    if (dec_persistent) WT_CUDA_OK(cudaMemcpyAsync(st, pd_status, sizeof(st), cudaMemcpyDeviceToHost, stream));
     WT_CUDA_OK(cudaStreamSynchronize(stream));
+    if (st[0] != 0) return fail(WT_ERR_CUDA, "persistent decoder abandoned a grid barrier (CTAs not co-resident?)");
     for (int b = 0; b < n_clips; ++b) {
       for (int i = 0; i < max_total; ++i) ids[(size_t)b * max_total + i] = ht[(size_t)b * 32 + i];
       lens_o[b] = hl[b];
