@@ -193,7 +193,11 @@ def run_gpu(args):
 
     B = CLIPS_PER_GPU
     eng = capi.Engine(wpath, device=local, max_batch=B, precision=capi.PRECISION_BF16)
-    stream = torch.cuda.current_stream()
+    # a dedicated (non-default) stream: the engine enqueues on it and the CUDA events below are recorded on it
+    # (wt_set_stream(NULL) would select the engine's own stream, which torch's events cannot see)
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     eng.set_stream(stream.cuda_stream)
     # every rank gets its own clips (global clip index = rank*B + i), 2 rotating sets so no step re-reads warm inputs
     sets = [synth.synth_pcm(B, seed=1000 * s + rank) for s in range(2)]

@@ -128,6 +128,11 @@ WT_API const char* wt_version(void);
 WT_API int wt_debug_gemm_bf16(void* cuda_stream, const void* A, const void* W, const float* bias, void* C, int M, int N,
                               int K, int flags);
 
+/* Engines created with WT_DEC_TRACE=1 in the environment: nanoseconds per phase kind of the persistent decoder as
+ * seen by CTA 0, accumulated over launches. out32[k] = phase k total (0 init, 1..8 the layer phases, 9 logits,
+ * 10 finalize+embed), out32[16+k] = the part of it spent waiting in the grid barrier. */
+WT_API int wt_debug_decoder_trace(wt_engine* e, uint64_t* out32, int reset);
+
 #ifdef __cplusplus
 }
 #endif

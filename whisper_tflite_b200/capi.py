@@ -27,7 +27,7 @@ EXPORTED = [
     "wt_engine_create", "wt_engine_destroy", "wt_engine_dims", "wt_set_mel_filters", "wt_set_stream",
     "wt_synchronize", "wt_log_mel", "wt_encode", "wt_decode_greedy", "wt_transcribe_tokens",
     "wt_get_step_logits", "wt_launch_count", "wt_last_error", "wt_version", "wt_debug_gemm_bf16",
-    "wt_profile_enable", "wt_profile_read", "wt_stage_count", "wt_stage_name",
+    "wt_profile_enable", "wt_profile_read", "wt_stage_count", "wt_stage_name", "wt_debug_decoder_trace",
 ]
 
 
@@ -194,6 +194,14 @@ class Engine:
         cnt = (ctypes.c_int32 * n)()
         _check(self.lib.wt_profile_read(self.h, ms, cnt, n))
         return {self.lib.wt_stage_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n)}
+
+    def decoder_trace(self, reset: bool = True):
+        """WT_DEC_TRACE=1 engines: {phase: (total us, barrier-wait us)} of the persistent decoder as seen by CTA 0."""
+        names = ["init", "ln1_qkv", "self_attn", "out_proj", "lnx_xq", "cross_attn", "xout_proj", "ln2_fc1", "fc2",
+                 "logits", "finalize_embed"]
+        buf = (ctypes.c_uint64 * 32)()
+        _check(self.lib.wt_debug_decoder_trace(self.h, buf, int(reset)))
+        return {n: (buf[i] / 1e3, buf[16 + i] / 1e3) for i, n in enumerate(names)}
 
     def step_logits(self, step: int, n_clips: int) -> np.ndarray:
         out = np.empty((n_clips, self.dims.n_vocab), dtype=np.float32)

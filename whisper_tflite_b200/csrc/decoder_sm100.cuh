@@ -33,7 +33,9 @@ namespace wt {
 
 constexpr int kDecThreads = 512;
 constexpr int kDecWarps = kDecThreads / 32;
-constexpr int kDecMaxClips = 64;   // rows of one clip group (4 m-tiles of 16)
+constexpr int kDecGroupMax = 16;   // clips owned by one cluster: rows of one staged A tile (kDecMT m-tiles of 16)
+constexpr int kDecMT = kDecGroupMax / 16;
+constexpr int kDecMaxCluster = 16; // CTAs per cluster (non-portable size; 8 is the portable fallback)
 constexpr int kDecMaxD = 768;      // d_model ceiling of this kernel (tiny 384, base 512, small 768)
 constexpr int kDecTokStride = 32;
 
@@ -52,6 +54,8 @@ struct DecLayerDev {
 struct DecParams {
   const DecLayerDev* layers;
   int n_layers, n_clips, clip0, d, H, S, V;
+  int group_clips;                // clips owned by one cluster (<= kDecGroupMax)
+  int rank, G;                    // filled in by the kernel: CTA rank in its cluster, cluster size
   const __nv_bfloat16* tok_emb;   // [V][d] (also the tied logits matrix)
   const __nv_bfloat16* pos_emb;   // [n_text_ctx][d]
   const float *lnf_g, *lnf_b;
@@ -67,18 +71,19 @@ struct DecParams {
   float* xpart;                   // [pairs][xslots][66] cross-attention partials (acc[64], max, sum)
   unsigned* xtickets;             // [pairs]
   int xslots;
-  unsigned long long* amax_part;  // [64][gridDim.x]
+  unsigned long long* amax_part;  // [group][kDecGroupMax][cluster size]
   float* step_logits;             // optional [steps][max_batch][V]
   long long step_logits_stride;   // max_batch * V
-  unsigned* bar;                  // grid barrier counter, zeroed before launch
-  int* status;                    // [0] error flag (barrier timeout), [1] number of finished clips
+  int* finished;                  // [n_groups] number of clips of the group that produced EOT (zeroed before launch)
+  unsigned long long* trace;      // optional [32]: ns per phase kind seen by cluster 0 / CTA 0 ([k] total, [16+k] barrier wait)
 };
 
 struct DecSmem {
   static constexpr int kAStride = 2 * kDecMaxD + 64;            // bytes per staged row (== 64 mod 128: conflict-free LDS.128)
   static constexpr int kA = 0;
-  static constexpr int kRed = kA + kDecMaxClips * kAStride;     // [16 warps][64][8] f32
-  static constexpr int kMisc = kRed + kDecWarps * 64 * 8 * 4;   // sq / cross-merge / argmax scratch
+  static constexpr int kRedPerWarp = kDecMT * 16 * 8;           // floats
+  static constexpr int kRed = kA + kDecGroupMax * kAStride;     // [16 warps][kDecMT*16][8] f32
+  static constexpr int kMisc = kRed + kDecWarps * kRedPerWarp * 4;   // sq / cross-merge / argmax scratch
   static constexpr int kMiscBytes = kDecWarps * 66 * 4 + 64 * 8 + 64;
   static constexpr int kTotal = kMisc + ((kMiscBytes + 127) & ~127);
 };
@@ -133,33 +138,40 @@ __device__ __forceinline__ void bf16x8_to_f32(const uint4& v, float* f) {
   }
 }
 
-// All CTAs of the (cooperative) grid. Data written before the barrier by any CTA is visible after it to loads that
-// bypass L1 (__ldcg) — every inter-CTA buffer in this kernel is read that way. Returns false when the launch is
-// being abandoned (a CTA waited ~2 s: lost co-residency must not hang the device); callers return at once.
-__device__ __forceinline__ bool dec_grid_sync(const DecParams& p, unsigned& target) {
-  __shared__ int s_ok;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    target += gridDim.x;
-    __threadfence();
-    atomicAdd(p.bar, 1u);
-    const long long t0 = clock64();
-    int ok = 1;
-    unsigned it = 0;
-    while (ld_acquire_u32(p.bar) < target) {
-      if ((++it & 255u) == 0u) {
-        if (clock64() - t0 > 4000000000ll) atomicExch(p.status, 1);
-        if (__ldcg(p.status) != 0) {
-          ok = 0;
-          break;
-        }
-      }
-    }
-    __threadfence();
-    s_ok = ok;
+// All CTAs of one cluster (hardware barrier, release/acquire at cluster scope). A cluster owns its clips for the whole
+// loop, so nothing in this kernel ever waits on another cluster: no cooperative launch, no software grid barrier.
+// Inter-CTA buffers live in global memory (L2) and are read with loads that bypass L1 (__ldcg).
+__device__ __forceinline__ unsigned long long dec_globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ unsigned dec_cluster_ctarank() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ unsigned dec_cluster_nctarank() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ unsigned dec_clusterid_x() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void dec_cluster_sync(const DecParams& p, int kind, unsigned long long& tlast) {
+  const bool tr = p.trace != nullptr && threadIdx.x == 0;
+  const unsigned long long t_arr = tr ? dec_globaltimer() : 0ull;
+  __threadfence();
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (tr) {
+    const unsigned long long t = dec_globaltimer();
+    p.trace[kind] += t - tlast;
+    p.trace[16 + kind] += t - t_arr;
+    tlast = t;
   }
-  __syncthreads();
-  return s_ok != 0;
 }
 
 // ---- A staging: all n_rows (padded to 16) x d into shared memory as bf16, row stride DecSmem::kAStride ----
@@ -225,7 +237,7 @@ __device__ __forceinline__ void dec_stage_bf16(uint8_t* sA, const __nv_bfloat16*
 
 // acc[mt][0..3] += A[mt*16 + {g, g+8}][kb-range] . W[n0 + g][kb-range]   (one warp: 64 x 8 outputs)
 __device__ __forceinline__ void dec_warp_mma(const uint8_t* sA, const __nv_bfloat16* wrow, bool row_ok, int kb0, int kb1,
-                                             int n_mt, float (&acc)[4][4]) {
+                                             int n_mt, float (&acc)[kDecMT][4]) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const uint8_t* a_base = sA + (size_t)g * DecSmem::kAStride + t * 16;
   for (int kb = kb0; kb < kb1; kb += 4) {
@@ -239,7 +251,7 @@ __device__ __forceinline__ void dec_warp_mma(const uint8_t* sA, const __nv_bfloa
     for (int u = 0; u < 4; ++u) {
       if (kb + u < kb1) {
 #pragma unroll
-        for (int mt = 0; mt < 4; ++mt) {
+        for (int mt = 0; mt < kDecMT; ++mt) {
           if (mt < n_mt) {
             const uint8_t* ap = a_base + (size_t)(mt * 16) * DecSmem::kAStride + (kb + u) * 64;
             const uint4 lo = *reinterpret_cast<const uint4*>(ap);
@@ -253,8 +265,8 @@ __device__ __forceinline__ void dec_warp_mma(const uint8_t* sA, const __nv_bfloa
   }
 }
 
-__device__ __forceinline__ int dec_pick_ksplit(int n_groups, int kblocks) {
-  const int gpc = (n_groups + (int)gridDim.x - 1) / (int)gridDim.x;
+__device__ __forceinline__ int dec_pick_ksplit(int n_groups, int kblocks, int G) {
+  const int gpc = (n_groups + G - 1) / G;
   const int maxk = kDecWarps / (gpc < kDecWarps ? gpc : kDecWarps);
   int best = 1;
   for (int k = 2; k <= maxk && k <= 8; ++k)
@@ -272,20 +284,20 @@ __device__ __forceinline__ void dec_gemm(uint8_t* smem, const DecParams& p, cons
   const int d = p.d, K = n_chunks * d, kblocks = d >> 5;
   const int n_mt = (p.n_clips + 15) >> 4;
   const int n_groups = (N + 7) >> 3;
-  const int ksplit = dec_pick_ksplit(n_groups, kblocks);
+  const int ksplit = dec_pick_ksplit(n_groups, kblocks, p.G);
   const int teams = kDecWarps / ksplit;
   const int team = warp / ksplit, kpart = warp - team * ksplit;
   const bool team_ok = team < teams;
-  const int gpc = (n_groups + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int gpc = (n_groups + p.G - 1) / p.G;
   const int rounds = (gpc + teams - 1) / teams;
   const int kb_per = kblocks / ksplit;
   for (int round = 0; round < rounds; ++round) {
-    const int grp = (int)blockIdx.x + (int)gridDim.x * (round * teams + team);
+    const int grp = p.rank + p.G * (round * teams + team);
     const bool active = team_ok && grp < n_groups;
     const int n0 = grp * 8;
-    float acc[4][4];
+    float acc[kDecMT][4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < kDecMT; ++i)
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
     for (int chunk = 0; chunk < n_chunks; ++chunk) {
@@ -301,9 +313,10 @@ __device__ __forceinline__ void dec_gemm(uint8_t* smem, const DecParams& p, cons
       }
     }
     // cross-warp (k-split) reduction through shared memory, then the epilogue by the whole team
-    float* mine = red + warp * 512;
+    constexpr int kRW = DecSmem::kRedPerWarp;
+    float* mine = red + warp * kRW;
 #pragma unroll
-    for (int mt = 0; mt < 4; ++mt) {
+    for (int mt = 0; mt < kDecMT; ++mt) {
       *reinterpret_cast<float2*>(mine + (mt * 16 + g) * 8 + 2 * t) = make_float2(acc[mt][0], acc[mt][1]);
       *reinterpret_cast<float2*>(mine + (mt * 16 + g + 8) * 8 + 2 * t) = make_float2(acc[mt][2], acc[mt][3]);
     }
@@ -313,13 +326,13 @@ __device__ __forceinline__ void dec_gemm(uint8_t* smem, const DecParams& p, cons
       __syncwarp();
     }
     if (active) {
-      const float* base = red + team * ksplit * 512;
+      const float* base = red + team * ksplit * kRW;
       const int tt = kpart * 32 + lane, nt = ksplit * 32;
-      for (int idx = tt; idx < 512; idx += nt) {
+      for (int idx = tt; idx < kRW; idx += nt) {
         const int r = idx >> 3, c = idx & 7;
         if (r < p.n_clips && n0 + c < N) {
           float v = 0.0f;
-          for (int k = 0; k < ksplit; ++k) v += base[k * 512 + idx];
+          for (int k = 0; k < ksplit; ++k) v += base[k * kRW + idx];
           epi(r, n0 + c, v);
         }
       }
@@ -333,21 +346,45 @@ __device__ __forceinline__ void dec_gemm(uint8_t* smem, const DecParams& p, cons
 }
 
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kDecThreads, 1) decoder_persistent_kernel(DecParams p) {
+__global__ void __launch_bounds__(kDecThreads, 1) decoder_persistent_kernel(const DecParams p_in) {
   extern __shared__ __align__(128) uint8_t dec_smem[];
   uint8_t* sA = dec_smem + DecSmem::kA;
   float* s_misc = reinterpret_cast<float*>(dec_smem + DecSmem::kMisc);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int G = gridDim.x;
+  // this cluster's view: its clip group, its slices of the scratch buffers
+  DecParams p = p_in;
+  const int G = (int)dec_cluster_nctarank();
+  const int rank = (int)dec_cluster_ctarank();
+  const int group = (int)dec_clusterid_x();
+  p.G = G;
+  p.rank = rank;
+  {
+    const int gc = p_in.group_clips;
+    const int first = group * gc;
+    p.clip0 = p_in.clip0 + first;
+    p.n_clips = (p_in.n_clips - first < gc) ? p_in.n_clips - first : gc;
+    if (p.n_clips <= 0) return;  // whole cluster leaves together
+    const size_t row0 = (size_t)group * kDecGroupMax;
+    p.x += row0 * p.d;
+    p.qs += row0 * p.d;
+    p.att += row0 * p.d;
+    p.qx += row0 * p.d;
+    p.hmid += row0 * 4 * p.d;
+    p.xpart += row0 * p.H * (size_t)p.xslots * 66;
+    p.xtickets += row0 * p.H;
+    p.amax_part += row0 * kDecMaxCluster;
+    p.finished += group;
+    if (group != 0 || rank != 0) p.trace = nullptr;
+  }
   const int d = p.d, H = p.H, S = p.S, V = p.V, B = p.n_clips;
   const int rows_pad = ((B + 15) >> 4) << 4;
   const int n_mt = rows_pad >> 4;
-  unsigned bar_target = 0;
+  unsigned long long tlast = (p.trace != nullptr && threadIdx.x == 0) ? dec_globaltimer() : 0ull;
   const uint64_t pol_stream = l2_evict_first_policy();
 
   // x[b] = tok_emb[token(b, pos)] + pos_emb[pos]  (CTA b; a finished clip keeps stepping on token 0, unused)
   auto embed = [&](int pos) {
-    for (int b = blockIdx.x; b < B; b += G) {
+    for (int b = rank; b < B; b += G) {
       int tok = __ldcg(p.tokens + (size_t)(p.clip0 + b) * kDecTokStride + pos);
       if (tok < 0) tok = 0;
       const __nv_bfloat16* te = p.tok_emb + (size_t)tok * d;
@@ -357,14 +394,14 @@ __global__ void __launch_bounds__(kDecThreads, 1) decoder_persistent_kernel(DecP
   };
 
   // ---- init: token rows, lens, done (CTA b), first embedding ----
-  for (int b = blockIdx.x; b < B; b += G) {
+  for (int b = rank; b < B; b += G) {
     if (tid == 0) {
       p.lens[p.clip0 + b] = p.prompt_len;
       p.done[p.clip0 + b] = 0;
     }
   }
   embed(0);
-  if (!dec_grid_sync(p, bar_target)) return;
+  dec_cluster_sync(p, 0, tlast);
 
   for (int pos = 0; pos <= p.max_total - 2; ++pos) {
     for (int l = 0; l < p.n_layers; ++l) {
@@ -381,11 +418,11 @@ __global__ void __launch_bounds__(kDecThreads, 1) decoder_persistent_kernel(DecP
                    cache[(((size_t)(p.clip0 + r) * H + (c >> 6)) * 32 + pos) * 64 + (c & 63)] = __float2bfloat16(v);
                  }
                });
-      if (!dec_grid_sync(p, bar_target)) return;
+      dec_cluster_sync(p, 1, tlast);
       // ---- 2. self-attention over cache rows 0..pos: one warp per (clip, head), lane = key ----
       {
         float* sq = s_misc + warp * 64;
-        for (int pr = blockIdx.x * kDecWarps + warp; pr < B * H; pr += G * kDecWarps) {
+        for (int pr = rank * kDecWarps + warp; pr < B * H; pr += G * kDecWarps) {
           const int b = pr / H, h = pr - b * H;
           const float2 q2 = __ldcg(reinterpret_cast<const float2*>(p.qs + (size_t)b * d + h * 64 + 2 * lane));
           sq[2 * lane] = q2.x * 0.125f;
@@ -419,23 +456,23 @@ __global__ void __launch_bounds__(kDecThreads, 1) decoder_persistent_kernel(DecP
           __syncwarp();
         }
       }
-      if (!dec_grid_sync(p, bar_target)) return;
+      dec_cluster_sync(p, 2, tlast);
       // ---- 3. out-proj + residual ----
       dec_gemm(dec_smem, p, L.w_out, d, 1, [&](int) { dec_stage_f32(sA, p.att, d, B, rows_pad, d); },
                [&](int r, int n, float v) {
                  float* xp = p.x + (size_t)r * d + n;
                  *xp = __ldcg(xp) + v + __ldg(L.b_out + n);
                });
-      if (!dec_grid_sync(p, bar_target)) return;
+      dec_cluster_sync(p, 3, tlast);
       // ---- 4. LNx -> cross-attention query ----
       dec_gemm(dec_smem, p, L.w_xq, d, 1, [&](int) { dec_stage_ln(sA, p.x, L.lnx_g, L.lnx_b, B, rows_pad, d); },
                [&](int r, int n, float v) { p.qx[(size_t)r * d + n] = v + __ldg(L.b_xq + n); });
-      if (!dec_grid_sync(p, bar_target)) return;
-      // ---- 5. cross-attention: the (clip, head, key) space is cut into gridDim equal contiguous ranges ----
+      dec_cluster_sync(p, 4, tlast);
+      // ---- 5. cross-attention: the group's (clip, head, key) space is cut into one contiguous range per CTA ----
       {
         const long long T = (long long)B * H * S;
         const long long per = (T + G - 1) / G;
-        long long cur = (long long)blockIdx.x * per;
+        long long cur = (long long)rank * per;
         const long long hi = (cur + per < T) ? cur + per : T;
         const int grp = lane >> 3, sub = lane & 7;
         float* sm_m = s_misc;               // [16]
@@ -534,7 +571,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) decoder_persistent_kernel(DecP
           // slot of this CTA among the CTAs that cover pair `pr`
           const int first_cta = (int)(((long long)pr * S) / per);
           const int last_cta = (int)((((long long)pr + 1) * S - 1) / per);
-          const int slot = (int)blockIdx.x - first_cta;
+          const int slot = rank - first_cta;
           float* pp = p.xpart + ((size_t)pr * p.xslots + slot) * 66;
           if (tid < 64) {
             float M = sm_m[0];
@@ -580,25 +617,25 @@ __global__ void __launch_bounds__(kDecThreads, 1) decoder_persistent_kernel(DecP
           cur += bnd - a;
         }
       }
-      if (!dec_grid_sync(p, bar_target)) return;
+      dec_cluster_sync(p, 5, tlast);
       // ---- 6. cross out-proj + residual ----
       dec_gemm(dec_smem, p, L.w_xout, d, 1, [&](int) { dec_stage_f32(sA, p.att, d, B, rows_pad, d); },
                [&](int r, int n, float v) {
                  float* xp = p.x + (size_t)r * d + n;
                  *xp = __ldcg(xp) + v + __ldg(L.b_xout + n);
                });
-      if (!dec_grid_sync(p, bar_target)) return;
+      dec_cluster_sync(p, 6, tlast);
       // ---- 7. LN2 -> fc1 -> GELU ----
       dec_gemm(dec_smem, p, L.w_fc1, 4 * d, 1, [&](int) { dec_stage_ln(sA, p.x, L.ln2_g, L.ln2_b, B, rows_pad, d); },
                [&](int r, int n, float v) { p.hmid[(size_t)r * 4 * d + n] = __float2bfloat16(gelu_erf(v + __ldg(L.b_fc1 + n))); });
-      if (!dec_grid_sync(p, bar_target)) return;
+      dec_cluster_sync(p, 7, tlast);
       // ---- 8. fc2 + residual (K = 4d in 4 staged chunks) ----
       dec_gemm(dec_smem, p, L.w_fc2, d, 4, [&](int chunk) { dec_stage_bf16(sA, p.hmid + (size_t)chunk * d, 4 * d, B, rows_pad, d); },
                [&](int r, int n, float v) {
                  float* xp = p.x + (size_t)r * d + n;
                  *xp = __ldcg(xp) + v + __ldg(L.b_fc2 + n);
                });
-      if (!dec_grid_sync(p, bar_target)) return;
+      dec_cluster_sync(p, 8, tlast);
     }
 
     const bool want_logits = pos >= p.prompt_len - 1;
@@ -606,28 +643,28 @@ __global__ void __launch_bounds__(kDecThreads, 1) decoder_persistent_kernel(DecP
       // ---- final LN -> tied logits with fused (max, last index) per row ----
       unsigned long long* s_best = reinterpret_cast<unsigned long long*>(dec_smem + DecSmem::kRed);
       __syncthreads();
-      for (int i = tid; i < kDecMaxClips; i += kDecThreads) s_best[i] = 0ull;
+      for (int i = tid; i < kDecGroupMax; i += kDecThreads) s_best[i] = 0ull;
       dec_stage_ln(sA, p.x, p.lnf_g, p.lnf_b, B, rows_pad, d);
       __syncthreads();
       const int g = lane >> 2, t = lane & 3;
       const int n_groups = (V + 7) >> 3;
       const int step = pos - (p.prompt_len - 1);
       float* lg = p.step_logits ? p.step_logits + (size_t)step * p.step_logits_stride : nullptr;
-      unsigned long long best[4][2];
+      unsigned long long best[kDecMT][2];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) best[i][0] = best[i][1] = 0ull;
-      for (int grp = (int)blockIdx.x + G * warp; grp < n_groups; grp += G * kDecWarps) {
+      for (int i = 0; i < kDecMT; ++i) best[i][0] = best[i][1] = 0ull;
+      for (int grp = rank + G * warp; grp < n_groups; grp += G * kDecWarps) {
         const int n0 = grp * 8;
-        float acc[4][4];
+        float acc[kDecMT][4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+        for (int i = 0; i < kDecMT; ++i)
 #pragma unroll
           for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
         const bool row_ok = n0 + g < V;
         dec_warp_mma(sA, p.tok_emb + (size_t)(row_ok ? n0 + g : 0) * d, row_ok, 0, d >> 5, n_mt, acc);
         const int c0 = n0 + 2 * t;
 #pragma unroll
-        for (int mt = 0; mt < 4; ++mt) {
+        for (int mt = 0; mt < kDecMT; ++mt) {
           if (mt < n_mt) {
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) {
@@ -647,7 +684,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) decoder_persistent_kernel(DecP
         }
       }
 #pragma unroll
-      for (int mt = 0; mt < 4; ++mt)
+      for (int mt = 0; mt < kDecMT; ++mt)
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {
           unsigned long long v = best[mt][hh];
@@ -656,11 +693,11 @@ __global__ void __launch_bounds__(kDecThreads, 1) decoder_persistent_kernel(DecP
           if (t == 0 && v != 0ull) atomicMax(s_best + mt * 16 + g + hh * 8, v);
         }
       __syncthreads();
-      for (int r = tid; r < B; r += kDecThreads) p.amax_part[(size_t)r * G + blockIdx.x] = s_best[r];
-      if (!dec_grid_sync(p, bar_target)) return;
+      for (int r = tid; r < B; r += kDecThreads) p.amax_part[(size_t)r * G + rank] = s_best[r];
+      dec_cluster_sync(p, 9, tlast);
     }
     // ---- finalize (CTA b): append the winner, EOT bookkeeping; then embed the next position ----
-    for (int b = blockIdx.x; b < B; b += G) {
+    for (int b = rank; b < B; b += G) {
       if (want_logits) {
         unsigned long long* s_red = reinterpret_cast<unsigned long long*>(s_misc);
         unsigned long long v = 0ull;
@@ -678,7 +715,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) decoder_persistent_kernel(DecP
             p.lens[cb] = pos + 2;
             if (tok == p.eot) {
               p.done[cb] = 1;
-              atomicAdd(p.status + 1, 1);
+              atomicAdd(p.finished, 1);
             }
           }
           __threadfence();
@@ -687,8 +724,8 @@ __global__ void __launch_bounds__(kDecThreads, 1) decoder_persistent_kernel(DecP
       }
     }
     if (pos + 1 <= p.max_total - 2) embed(pos + 1);
-    if (!dec_grid_sync(p, bar_target)) return;
-    if (__ldcg(p.status + 1) >= B) break;  // every clip has produced EOT (whisper.cpp:397-399, per clip)
+    dec_cluster_sync(p, 10, tlast);
+    if (__ldcg(p.finished) >= B) break;  // every clip has produced EOT (whisper.cpp:397-399, per clip)
   }
 }
 

@@ -266,15 +266,16 @@ struct wt_engine {
   unsigned* xa_tickets = nullptr;
   unsigned long long* argmax_part = nullptr;
   int *tokens = nullptr, *lens = nullptr, *done = nullptr, *d_prompt = nullptr;
-  // persistent decoder (bf16, d_model <= 768): one cooperative launch per group of <= 64 clips
+  // persistent decoder (bf16, d_model <= 768): one launch, one thread-block cluster per group of clips
   bool dec_persistent = false;
-  int dec_grid = 0;
+  int dec_cluster = 0, dec_group = 0, dec_groups_cap = 0, dec_active_clusters = 0;
   wt::DecLayerDev* d_dec_layers = nullptr;
   float *pd_x = nullptr, *pd_qs = nullptr, *pd_att = nullptr, *pd_qx = nullptr, *pd_xpart = nullptr;
   bf16* pd_hmid = nullptr;
-  unsigned *pd_xtickets = nullptr, *pd_bar = nullptr;
+  unsigned* pd_xtickets = nullptr;
   unsigned long long* pd_amax = nullptr;
-  int* pd_status = nullptr;
+  int* pd_finished = nullptr;
+  unsigned long long* pd_trace = nullptr;  // WT_DEC_TRACE=1: per-phase ns of the persistent decoder (CTA 0)
   int pd_xslots_cap = 0;
   int enc_clips = 0;  // clips whose encoder states / cross K,V are resident
   std::map<std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint64_t, uint64_t, uint32_t>, CUtensorMap> map_cache;
@@ -706,18 +707,45 @@ int wt_engine::load_model(const char* path) {
   return init_persistent_decoder();
 }
 
-// The persistent decoder needs every CTA co-resident (grid barriers): cooperative launch, one CTA per SM.
+// The persistent decoder: one thread-block cluster per group of clips, every cluster independent of the others
+// (hardware cluster barriers only), so a plain launch with a cluster dimension — any number of groups queue up.
 int wt_engine::init_persistent_decoder() {
   const char* ov = getenv("WT_DECODER");
   if (f32mode() || dims.d_model > wt::kDecMaxD || (ov && strcmp(ov, "legacy") == 0)) return WT_OK;
-  int coop = 0;
-  WT_CUDA_OK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device));
-  if (!coop) return WT_OK;
   WT_CUDA_OK(cudaFuncSetAttribute(wt::decoder_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::DecSmem::kTotal));
-  int per_sm = 0;
-  WT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wt::decoder_persistent_kernel, wt::kDecThreads, wt::DecSmem::kTotal));
-  if (per_sm < 1) return fail(WT_ERR_CUDA, "decoder_persistent_kernel does not fit one CTA per SM");
-  dec_grid = num_sms;
+  // cluster shape: 16 CTAs x 8 clips (8 clusters fill 128 SMs at B = 64) when the device can co-schedule a 16-CTA
+  // cluster per GPC, else the portable 8 CTAs x 4 clips. WT_DEC_CLUSTER / WT_DEC_GROUP override (probing).
+  dec_cluster = 0;
+  const int want[2] = {16, 8};
+  const char* ocl = getenv("WT_DEC_CLUSTER");
+  for (int i = 0; i < 2 && !dec_cluster; ++i) {
+    const int cs = ocl ? atoi(ocl) : want[i];
+    if (cs < 1 || cs > wt::kDecMaxCluster) return fail(WT_ERR_INVALID, "WT_DEC_CLUSTER must be in [1, %d]", wt::kDecMaxCluster);
+    if (cs > 8) {
+      if (cudaFuncSetAttribute(wt::decoder_persistent_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+        cudaGetLastError();
+        if (ocl) return fail(WT_ERR_CUDA, "cluster size %d is not allowed on this device", cs);
+        continue;
+      }
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(cs);
+    cfg.blockDim = dim3(wt::kDecThreads);
+    cfg.dynamicSmemBytes = wt::DecSmem::kTotal;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    int n_active = 0;
+    if (cudaOccupancyMaxActiveClusters(&n_active, wt::decoder_persistent_kernel, &cfg) != cudaSuccess) { cudaGetLastError(); n_active = 0; }
+    if (n_active >= 1) { dec_cluster = cs; dec_active_clusters = n_active; }
+    if (ocl) break;
+  }
+  if (!dec_cluster) return fail(WT_ERR_CUDA, "decoder_persistent_kernel: no schedulable cluster shape");
+  dec_group = dec_cluster >= 16 ? 8 : 4;
+  if (const char* og = getenv("WT_DEC_GROUP")) dec_group = atoi(og);
+  if (dec_group < 1 || dec_group > wt::kDecGroupMax) return fail(WT_ERR_INVALID, "WT_DEC_GROUP must be in [1, %d]", wt::kDecGroupMax);
   const int d = dims.d_model, H = dims.n_heads, S = dims.n_audio_ctx;
   std::vector<wt::DecLayerDev> hl(dims.n_dec_layers);
   for (int i = 0; i < dims.n_dec_layers; ++i) {
@@ -735,60 +763,78 @@ int wt_engine::init_persistent_decoder() {
   }
   WT_TRY(alloc(&d_dec_layers, hl.size()));
   WT_CUDA_OK(cudaMemcpy(d_dec_layers, hl.data(), hl.size() * sizeof(wt::DecLayerDev), cudaMemcpyHostToDevice));
-  const size_t R = wt::kDecMaxClips;
+  dec_groups_cap = (max_batch + dec_group - 1) / dec_group;
+  const size_t R = (size_t)dec_groups_cap * wt::kDecGroupMax;  // scratch rows: kDecGroupMax per group
   WT_TRY(alloc(&pd_x, R * d));
   WT_TRY(alloc(&pd_qs, R * d));
   WT_TRY(alloc(&pd_att, R * d));
   WT_TRY(alloc(&pd_qx, R * d));
   WT_TRY(alloc(&pd_hmid, R * 4 * d));
-  // worst case slots per (clip, head): one clip in flight -> per = ceil(H*S/grid) keys per CTA
-  const long long per_min = ((long long)H * S + dec_grid - 1) / dec_grid;
+  // worst case slots per (clip, head): a group holding one clip -> per = ceil(H*S/cluster) keys per CTA
+  const long long per_min = ((long long)H * S + dec_cluster - 1) / dec_cluster;
   pd_xslots_cap = (int)((S + per_min - 1) / per_min) + 1;
   WT_TRY(alloc(&pd_xpart, R * H * (size_t)pd_xslots_cap * 66));
   WT_TRY(alloc(&pd_xtickets, R * H, true));
-  WT_TRY(alloc(&pd_amax, R * (size_t)dec_grid));
-  WT_TRY(alloc(&pd_bar, 4, true));
-  WT_TRY(alloc(&pd_status, 4, true));
+  WT_TRY(alloc(&pd_amax, R * (size_t)wt::kDecMaxCluster));
+  WT_TRY(alloc(&pd_finished, (size_t)dec_groups_cap, true));
+  if (const char* tr = getenv("WT_DEC_TRACE")) {
+    if (tr[0] == '1') WT_TRY(alloc(&pd_trace, 32, true));
+  }
   dec_persistent = true;
   return WT_OK;
 }
 
 int wt_engine::decode_persistent(int n_clips, int prompt_len, int max_total, int eot) {
   const int d = dims.d_model, H = dims.n_heads, S = dims.n_audio_ctx;
-  for (int c0 = 0; c0 < n_clips; c0 += wt::kDecMaxClips) {
-    const int nb = (n_clips - c0 < wt::kDecMaxClips) ? n_clips - c0 : wt::kDecMaxClips;
-    WT_CUDA_OK(cudaMemsetAsync(pd_bar, 0, 4 * sizeof(unsigned), stream));
-    WT_CUDA_OK(cudaMemsetAsync(pd_status, 0, 4 * sizeof(int), stream));
-    WT_CUDA_OK(cudaMemsetAsync(pd_xtickets, 0, (size_t)wt::kDecMaxClips * H * sizeof(unsigned), stream));
-    wt::DecParams p{};
-    p.layers = d_dec_layers;
-    p.n_layers = dims.n_dec_layers;
-    p.n_clips = nb;
-    p.clip0 = c0;
-    p.d = d; p.H = H; p.S = S; p.V = dims.n_vocab;
-    p.tok_emb = (const bf16*)tok_emb;
-    p.pos_emb = (const bf16*)dec_pos;
-    p.lnf_g = dec_ln.g; p.lnf_b = dec_ln.b;
-    p.tokens = tokens; p.lens = lens; p.done = done;
-    p.prompt_len = prompt_len; p.max_total = max_total; p.eot = eot;
-    p.x = pd_x; p.qs = pd_qs; p.att = pd_att; p.qx = pd_qx; p.hmid = pd_hmid;
-    p.xpart = pd_xpart; p.xtickets = pd_xtickets;
-    const long long per = ((long long)nb * H * S + dec_grid - 1) / dec_grid;
-    p.xslots = (int)((S + per - 1) / per) + 1;
-    if (p.xslots > pd_xslots_cap) return fail(WT_ERR_STATE, "cross-attention partial slots %d exceed capacity %d", p.xslots, pd_xslots_cap);
-    p.amax_part = pd_amax;
-    p.step_logits = keep_logits ? step_logits : nullptr;
-    p.step_logits_stride = (long long)max_batch * dims.n_vocab;
-    p.bar = pd_bar;
-    p.status = pd_status;
-    void* args[] = {&p};
-    stage = ST_DEC_PERSISTENT;
-    pre_launch();
-    WT_CUDA_OK(cudaLaunchCooperativeKernel((void*)wt::decoder_persistent_kernel, dim3(dec_grid), dim3(wt::kDecThreads), args,
-                                           (size_t)wt::DecSmem::kTotal, stream));
-    WT_TRY(check_launch("decoder_persistent_kernel"));
+  const int n_groups = (n_clips + dec_group - 1) / dec_group;
+  WT_CUDA_OK(cudaMemsetAsync(pd_finished, 0, (size_t)dec_groups_cap * sizeof(int), stream));
+  WT_CUDA_OK(cudaMemsetAsync(pd_xtickets, 0, (size_t)dec_groups_cap * wt::kDecGroupMax * H * sizeof(unsigned), stream));
+  wt::DecParams p{};
+  p.layers = d_dec_layers;
+  p.n_layers = dims.n_dec_layers;
+  p.n_clips = n_clips;
+  p.clip0 = 0;
+  p.group_clips = dec_group;
+  p.d = d; p.H = H; p.S = S; p.V = dims.n_vocab;
+  p.tok_emb = (const bf16*)tok_emb;
+  p.pos_emb = (const bf16*)dec_pos;
+  p.lnf_g = dec_ln.g; p.lnf_b = dec_ln.b;
+  p.tokens = tokens; p.lens = lens; p.done = done;
+  p.prompt_len = prompt_len; p.max_total = max_total; p.eot = eot;
+  p.x = pd_x; p.qs = pd_qs; p.att = pd_att; p.qx = pd_qx; p.hmid = pd_hmid;
+  p.xpart = pd_xpart; p.xtickets = pd_xtickets;
+  {
+    // slots per (clip, head) pair: the fullest and the last (smallest) group bound the range
+    int slots = 0;
+    const int last = n_clips - (n_groups - 1) * dec_group;
+    const int cand[2] = {n_groups > 1 ? dec_group : last, last};
+    for (int i = 0; i < 2; ++i) {
+      const long long per = ((long long)cand[i] * H * S + dec_cluster - 1) / dec_cluster;
+      const int sl = (int)((S + per - 1) / per) + 1;
+      if (sl > slots) slots = sl;
+    }
+    p.xslots = slots;
   }
-  return WT_OK;
+  if (p.xslots > pd_xslots_cap) return fail(WT_ERR_STATE, "cross-attention partial slots %d exceed capacity %d", p.xslots, pd_xslots_cap);
+  p.amax_part = pd_amax;
+  p.step_logits = keep_logits ? step_logits : nullptr;
+  p.step_logits_stride = (long long)max_batch * dims.n_vocab;
+  p.finished = pd_finished;
+  p.trace = pd_trace;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(n_groups * dec_cluster);
+  cfg.blockDim = dim3(wt::kDecThreads);
+  cfg.dynamicSmemBytes = wt::DecSmem::kTotal;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = dec_cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  stage = ST_DEC_PERSISTENT;
+  pre_launch();
+  WT_CUDA_OK(cudaLaunchKernelEx(&cfg, wt::decoder_persistent_kernel, p));
+  return check_launch("decoder_persistent_kernel");
 }
 
 // mel -> encoder states (+ cross-attention K/V of every decoder layer), all resident.
@@ -1065,10 +1111,7 @@ int wt_engine::copy_decode_results(int n_clips, int max_total, int32_t* ids, int
     std::vector<int> ht((size_t)n_clips * 32), hl(n_clips);
     WT_CUDA_OK(cudaMemcpyAsync(ht.data(), tokens, ht.size() * 4, cudaMemcpyDeviceToHost, stream));
     WT_CUDA_OK(cudaMemcpyAsync(hl.data(), lens, hl.size() * 4, cudaMemcpyDeviceToHost, stream));
-    int st[4] = {0, 0, 0, 0};
-    if (dec_persistent) WT_CUDA_OK(cudaMemcpyAsync(st, pd_status, sizeof(st), cudaMemcpyDeviceToHost, stream));
     WT_CUDA_OK(cudaStreamSynchronize(stream));
-    if (st[0] != 0) return fail(WT_ERR_CUDA, "persistent decoder abandoned a grid barrier (CTAs not co-resident?)");
     for (int b = 0; b < n_clips; ++b) {
       for (int i = 0; i < max_total; ++i) ids[(size_t)b * max_total + i] = ht[(size_t)b * 32 + i];
       lens_o[b] = hl[b];
@@ -1192,6 +1235,16 @@ int wt_get_step_logits(wt_engine* e, int step, int n_clips, float* out, int out_
 }
 
 int64_t wt_launch_count(const wt_engine* e) { return e ? e->launches : 0; }
+
+int wt_debug_decoder_trace(wt_engine* e, uint64_t* out32, int reset) {
+  if (!e || !out32) return fail(WT_ERR_INVALID, "null argument");
+  if (!e->pd_trace) return fail(WT_ERR_STATE, "engine was not created under WT_DEC_TRACE=1 (or the persistent decoder is off)");
+  cudaSetDevice(e->device);
+  WT_CUDA_OK(cudaStreamSynchronize(e->stream));
+  WT_CUDA_OK(cudaMemcpy(out32, e->pd_trace, 32 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  if (reset) WT_CUDA_OK(cudaMemset(e->pd_trace, 0, 32 * sizeof(uint64_t)));
+  return WT_OK;
+}
 
 int wt_profile_enable(wt_engine* e, int enable) {
   if (!e) return fail(WT_ERR_INVALID, "engine is null");
