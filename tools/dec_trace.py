@@ -21,9 +21,13 @@ lens = torch.empty(B, dtype=torch.int32, device="cuda")
 for _ in range(2):
     eng.transcribe_tokens(pcm, ids_out=ids, lens_out=lens)
 eng.decoder_trace(reset=True)
+eng.profile(True)
 eng.transcribe_tokens(pcm, ids_out=ids, lens_out=lens)
+st = eng.profile_read()
+eng.profile(False)
+print("stage ms:", {k: round(v[0], 3) for k, v in st.items() if v[1]})
 tr = eng.decoder_trace()
-tot = sum(v[0] for v in tr.values())
+tot = sum(v[0] for k, v in tr.items() if ":" not in k)
 print(f"decoder trace {size} B={B}: total {tot/1e3:.3f} ms")
 for k, (t, w) in tr.items():
     print(f"  {k:16s} {t:10.1f} us  ({100*t/tot:5.1f}%)  barrier wait {w:9.1f} us")

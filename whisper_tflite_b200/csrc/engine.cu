@@ -196,7 +196,7 @@ struct Lin {            // y = x . W^T + b
 };
 struct LNp { float* g = nullptr; float* b = nullptr; };
 struct EncLayer { LNp ln1, ln2; Lin qkv, out, fc1, fc2; };
-struct DecLayer { LNp ln1, lnx, ln2; Lin qkv, out, xq, xkv, xout, fc1, fc2; void *kx = nullptr, *vx = nullptr, *kc = nullptr, *vc = nullptr; };
+struct DecLayer { LNp ln1, lnx, ln2; Lin qkv, out, xq, xkv, xout, fc1, fc2; void *kx = nullptr, *vx = nullptr, *kc = nullptr, *vc = nullptr, *kvx = nullptr; };
 
 enum Stage {
   ST_MEL = 0, ST_MEL_LAYOUT, ST_CONV, ST_ENC_LN, ST_ENC_GEMM, ST_ENC_ATTN, ST_XKV, ST_DEC_EMBED, ST_DEC_LN, ST_DEC_GEMM,
@@ -214,6 +214,8 @@ struct wt_engine {
   bool profiling = false;
   bool decoding = false;       // which phase generic ops (linear / layernorm) are attributed to
   int gemm_stage = -1;         // override for the next linear() (conv stem, cross K/V, logits)
+  void *next_kv_k = nullptr, *next_kv_v = nullptr;  // EPI_SPLIT_KV destinations of the next gemm_bf16()
+  bool next_kv_chunked = false;
   int stage = ST_MEL;
   struct ProfRec { int stage; cudaEvent_t a, b; };
   std::vector<ProfRec> prof;
@@ -347,6 +349,7 @@ struct wt_engine {
   int decode(int n_clips, const int64_t* prompt, int prompt_len, int max_total, int64_t eot, int32_t* ids, int32_t* lens_o,
              int out_mem);
   int copy_decode_results(int n_clips, int max_total, int32_t* ids, int32_t* lens_o, int out_mem);
+  bool persistent_decoder_wanted() const;
   int init_persistent_decoder();
   int decode_persistent(int n_clips, int prompt_len, int max_total, int eot);
 
@@ -419,6 +422,14 @@ int wt_engine::gemm_bf16(const void* A, const uint64_t* a_dims, const uint64_t* 
   p.C = C;
   p.cmap = cmap;
   p.argmax_part = amax;
+  if (flags & wt::EPI_SPLIT_KV) {
+    p.kv_k = (bf16*)next_kv_k;
+    p.kv_v = (bf16*)next_kv_v;
+    p.kv_S = dims.n_audio_ctx;
+    p.kv_H = dims.n_heads;
+    p.kv_chunk = next_kv_chunked ? wt::kXaChunk : 0;
+    p.kv_cpp = (dims.n_audio_ctx + wt::kXaChunk - 1) / wt::kXaChunk;
+  }
   p.M = M;
   p.N = L.N;
   p.K = K_total;
@@ -658,6 +669,7 @@ int wt_engine::load_model(const char* path) {
   }
   dec.resize(dims.n_dec_layers);
   const size_t kv_elems = B * (size_t)H * S * 64;
+  const bool want_persistent = persistent_decoder_wanted();
   const size_t cache_elems = B * (size_t)H * 32 * 64;
   for (int i = 0; i < dims.n_dec_layers; ++i) {
     const std::string p = "decoder.blocks." + std::to_string(i);
@@ -672,8 +684,14 @@ int wt_engine::load_model(const char* path) {
     WT_TRY(up_ln(L.ln2, p + ".mlp_ln"));
     WT_TRY(up_plain(L.fc1, p + ".mlp.0", 4 * d, d, true));
     WT_TRY(up_plain(L.fc2, p + ".mlp.2", d, 4 * d, true));
-    WT_TRY(alloc_bytes(&L.kx, kv_elems * esz));
-    WT_TRY(alloc_bytes(&L.vx, kv_elems * esz));
+    if (want_persistent) {
+      // streaming layout of the persistent decoder: [clip][head][chunk][K rows | V rows] (decoder_sm100.cuh)
+      const size_t cpp = (size_t)(S + wt::kXaChunk - 1) / wt::kXaChunk;
+      WT_TRY(alloc_bytes(&L.kvx, B * (size_t)H * cpp * 2 * wt::kXaChunk * 64 * esz, true));
+    } else {
+      WT_TRY(alloc_bytes(&L.kx, kv_elems * esz));
+      WT_TRY(alloc_bytes(&L.vx, kv_elems * esz));
+    }
     WT_TRY(alloc_bytes(&L.kc, cache_elems * esz, true));
     WT_TRY(alloc_bytes(&L.vc, cache_elems * esz, true));
   }
@@ -709,9 +727,13 @@ int wt_engine::load_model(const char* path) {
 
 // The persistent decoder: one thread-block cluster per group of clips, every cluster independent of the others
 // (hardware cluster barriers only), so a plain launch with a cluster dimension — any number of groups queue up.
-int wt_engine::init_persistent_decoder() {
+bool wt_engine::persistent_decoder_wanted() const {
   const char* ov = getenv("WT_DECODER");
-  if (f32mode() || dims.d_model > wt::kDecMaxD || (ov && strcmp(ov, "legacy") == 0)) return WT_OK;
+  return !(f32mode() || dims.d_model > wt::kDecMaxD || (ov && strcmp(ov, "legacy") == 0));
+}
+
+int wt_engine::init_persistent_decoder() {
+  if (!persistent_decoder_wanted()) return WT_OK;
   WT_CUDA_OK(cudaFuncSetAttribute(wt::decoder_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::DecSmem::kTotal));
   // cluster shape: 16 CTAs x 8 clips (8 clusters fill 128 SMs at B = 64) when the device can co-schedule a 16-CTA
   // cluster per GPC, else the portable 8 CTAs x 4 clips. WT_DEC_CLUSTER / WT_DEC_GROUP override (probing).
@@ -758,7 +780,7 @@ int wt_engine::init_persistent_decoder() {
     o.w_xout = (const bf16*)L.xout.w; o.b_xout = L.xout.b;
     o.w_fc1 = (const bf16*)L.fc1.w; o.b_fc1 = L.fc1.b;
     o.w_fc2 = (const bf16*)L.fc2.w; o.b_fc2 = L.fc2.b;
-    o.kx = (const bf16*)L.kx; o.vx = (const bf16*)L.vx;
+    o.kvx = (const bf16*)L.kvx;
     o.kc = (bf16*)L.kc; o.vc = (bf16*)L.vc;
   }
   WT_TRY(alloc(&d_dec_layers, hl.size()));
@@ -770,15 +792,20 @@ int wt_engine::init_persistent_decoder() {
   WT_TRY(alloc(&pd_att, R * d));
   WT_TRY(alloc(&pd_qx, R * d));
   WT_TRY(alloc(&pd_hmid, R * 4 * d));
-  // worst case slots per (clip, head): a group holding one clip -> per = ceil(H*S/cluster) keys per CTA
-  const long long per_min = ((long long)H * S + dec_cluster - 1) / dec_cluster;
-  pd_xslots_cap = (int)((S + per_min - 1) / per_min) + 1;
+  // worst case slots per (clip, head): a group holding one clip -> per = ceil(H*cpp/cluster) chunks per CTA
+  const int cpp = (S + wt::kXaChunk - 1) / wt::kXaChunk;
+  const int per_min = (H * cpp + dec_cluster - 1) / dec_cluster;
+  pd_xslots_cap = (cpp + per_min - 1) / per_min + 1;
   WT_TRY(alloc(&pd_xpart, R * H * (size_t)pd_xslots_cap * 66));
   WT_TRY(alloc(&pd_xtickets, R * H, true));
   WT_TRY(alloc(&pd_amax, R * (size_t)wt::kDecMaxCluster));
   WT_TRY(alloc(&pd_finished, (size_t)dec_groups_cap, true));
   if (const char* tr = getenv("WT_DEC_TRACE")) {
-    if (tr[0] == '1') WT_TRY(alloc(&pd_trace, 32, true));
+    if (tr[0] == '1') {
+      WT_TRY(alloc(&pd_trace, 32, true));
+      fprintf(stderr, "[whisper_b200] persistent decoder: cluster %d CTAs x %d clips, %d clusters co-resident, smem %d B\n",
+              dec_cluster, dec_group, dec_active_clusters, (int)wt::DecSmem::kTotal);
+    }
   }
   dec_persistent = true;
   return WT_OK;
@@ -786,7 +813,13 @@ int wt_engine::init_persistent_decoder() {
 
 int wt_engine::decode_persistent(int n_clips, int prompt_len, int max_total, int eot) {
   const int d = dims.d_model, H = dims.n_heads, S = dims.n_audio_ctx;
-  const int n_groups = (n_clips + dec_group - 1) / dec_group;
+  // one wave: grow the group (up to kDecGroupMax clips) until every cluster of the launch is co-resident
+  int gsz = dec_group;
+  if (!getenv("WT_DEC_GROUP")) {
+    const int need = (n_clips + dec_active_clusters - 1) / dec_active_clusters;
+    if (need > gsz) gsz = need < wt::kDecGroupMax ? need : wt::kDecGroupMax;
+  }
+  const int n_groups = (n_clips + gsz - 1) / gsz;
   WT_CUDA_OK(cudaMemsetAsync(pd_finished, 0, (size_t)dec_groups_cap * sizeof(int), stream));
   WT_CUDA_OK(cudaMemsetAsync(pd_xtickets, 0, (size_t)dec_groups_cap * wt::kDecGroupMax * H * sizeof(unsigned), stream));
   wt::DecParams p{};
@@ -794,7 +827,8 @@ int wt_engine::decode_persistent(int n_clips, int prompt_len, int max_total, int
   p.n_layers = dims.n_dec_layers;
   p.n_clips = n_clips;
   p.clip0 = 0;
-  p.group_clips = dec_group;
+  p.group_clips = gsz;
+  if (const char* dbg = getenv("WT_DEC_DEBUG")) p.debug = atoi(dbg);
   p.d = d; p.H = H; p.S = S; p.V = dims.n_vocab;
   p.tok_emb = (const bf16*)tok_emb;
   p.pos_emb = (const bf16*)dec_pos;
@@ -806,11 +840,12 @@ int wt_engine::decode_persistent(int n_clips, int prompt_len, int max_total, int
   {
     // slots per (clip, head) pair: the fullest and the last (smallest) group bound the range
     int slots = 0;
-    const int last = n_clips - (n_groups - 1) * dec_group;
-    const int cand[2] = {n_groups > 1 ? dec_group : last, last};
+    const int last = n_clips - (n_groups - 1) * gsz;
+    const int cand[2] = {n_groups > 1 ? gsz : last, last};
+    const int cpp = (S + wt::kXaChunk - 1) / wt::kXaChunk;
     for (int i = 0; i < 2; ++i) {
-      const long long per = ((long long)cand[i] * H * S + dec_cluster - 1) / dec_cluster;
-      const int sl = (int)((S + per - 1) / per) + 1;
+      const int per = (cand[i] * H * cpp + dec_cluster - 1) / dec_cluster;
+      const int sl = (cpp + per - 1) / per + 1;
       if (sl > slots) slots = sl;
     }
     p.xslots = slots;
@@ -959,14 +994,20 @@ int wt_engine::encode(const float* mel, int n_clips, int mel_mem, float* states_
   for (int l = 0; l < dims.n_dec_layers; ++l) {
     DecLayer& L = dec[l];
     gemm_stage = ST_XKV;
+    if (!f32mode()) {
+      // the GEMM epilogue writes K and V straight into the per-head layout [clip][H][S][64]
+      next_kv_k = dec_persistent ? L.kvx : L.kx;
+      next_kv_v = L.vx;
+      next_kv_chunked = dec_persistent;
+      WT_TRY(linear(enc_out, M2, L.xkv, nullptr, wt::EPI_SPLIT_KV));
+      gemm_stage = -1;
+      continue;
+    }
     WT_TRY(linear(enc_out, M2, L.xkv, qkv, 0));
     gemm_stage = -1;
     stage = ST_XKV;
     pre_launch();
-    if (f32mode())
-      wt::split_heads_kv_kernel<float><<<num_sms * 4, 256, 0, stream>>>((const float*)qkv, (float*)L.kx, (float*)L.vx, n_clips, S, H);
-    else
-      wt::split_heads_kv_kernel<bf16><<<num_sms * 4, 256, 0, stream>>>((const bf16*)qkv, (bf16*)L.kx, (bf16*)L.vx, n_clips, S, H);
+    wt::split_heads_kv_kernel<float><<<num_sms * 4, 256, 0, stream>>>((const float*)qkv, (float*)L.kx, (float*)L.vx, n_clips, S, H);
     WT_TRY(check_launch("split_heads_kv_kernel"));
   }
   enc_clips = n_clips;

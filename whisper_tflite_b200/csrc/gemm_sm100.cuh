@@ -35,7 +35,7 @@ constexpr int kGemmBM = 128;
 constexpr int kGemmBK = 64;
 constexpr int kGemmThreads = 192;
 
-enum : int { EPI_ADD = 4, EPI_OUT_F32 = 16, EPI_ARGMAX = 32 };  // EPI_BIAS = 1, EPI_GELU = 2 shared with SIMT
+enum : int { EPI_ADD = 4, EPI_OUT_F32 = 16, EPI_ARGMAX = 32, EPI_SPLIT_KV = 64 };  // EPI_BIAS = 1, EPI_GELU = 2 shared with SIMT
 
 struct GemmBf16Params {
   const float* bias;               // [N] f32 or null
@@ -44,6 +44,13 @@ struct GemmBf16Params {
   void* C;                         // bf16 (or f32 with EPI_OUT_F32) via cmap; unused with EPI_ARGMAX alone
   RowMap cmap;
   unsigned long long* argmax_part; // [M][n_tiles_n] packed (value, index) (EPI_ARGMAX)
+  // EPI_SPLIT_KV: N = 2*H*64 columns (k | v) of row m = clip*kv_S + s go to kv_k / kv_v [clip][H][kv_S][64] — the
+  // per-head streams the decoder's cross-attention reads — instead of C
+  // kv_chunk > 0 selects the streaming layout of the persistent decoder instead: one buffer (kv_k), per (clip, head)
+  // pair kv_cpp chunks of kv_chunk keys, each chunk = [K rows | V rows] (kv_chunk * 128 bytes each), so a decode step
+  // pulls a chunk with ONE contiguous 2*kv_chunk*128-byte bulk copy
+  __nv_bfloat16 *kv_k, *kv_v;
+  int kv_S, kv_H, kv_chunk, kv_cpp;
   int M, N, K;
   int rows_per_batch;              // A-side batching (== M for a plain matrix)
   int tiles_per_batch;             // ceil(rows_per_batch / 128)
@@ -393,7 +400,7 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
             }
           }
           __syncwarp();
-        } else if (p.C != nullptr) {
+        } else if (p.C != nullptr || (p.flags & EPI_SPLIT_KV)) {
           // bf16 output: 32 cols = 64 bytes per row
 #pragma unroll
           for (int i = 0; i < 4; ++i)
@@ -409,8 +416,24 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
             const int col = n0 + c0 + pc * 8;
             if (rb < p.rows_per_batch && col < p.N) {
               const uint4 val = *reinterpret_cast<const uint4*>(scr + rr * S::kScratchRowBytes + pc * 16);
-              *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C) +
-                                        p.cmap.at(batch * p.rows_per_batch + rb) + col) = val;
+              if (p.flags & EPI_SPLIT_KV) {
+                const int mm = batch * p.rows_per_batch + rb;
+                const int clip = mm / p.kv_S, sq = mm - clip * p.kv_S;
+                const int dm = p.kv_H * 64;
+                const int which = col >= dm, cc = which ? col - dm : col;
+                __nv_bfloat16* dst;
+                if (p.kv_chunk > 0) {
+                  const int ch = sq / p.kv_chunk, kin = sq - ch * p.kv_chunk;
+                  dst = p.kv_k + ((((size_t)(clip * p.kv_H + (cc >> 6)) * p.kv_cpp + ch) * 2 + which) * p.kv_chunk + kin) * 64 +
+                        (cc & 63);
+                } else {
+                  dst = (which ? p.kv_v : p.kv_k) + (((size_t)(clip * p.kv_H + (cc >> 6)) * p.kv_S + sq) * 64 + (cc & 63));
+                }
+                *reinterpret_cast<uint4*>(dst) = val;
+              } else {
+                *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C) +
+                                          p.cmap.at(batch * p.rows_per_batch + rb) + col) = val;
+              }
             }
           }
           __syncwarp();
