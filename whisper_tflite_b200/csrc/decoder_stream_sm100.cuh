@@ -1,0 +1,933 @@
+// Streaming persistent greedy decoder for sm_100a (second design of the loop of Decoder::forward,
+// whisper.cpp:363-402): one launch, one thread-block cluster per group of <= 16 clips, and ONE producer warp per CTA
+// that feeds everything the CTA will ever read in bulk — its slices of the packed projection weights, its range of
+// the cross-attention K/V stream, its slice of the tied logits matrix — through a single shared-memory ring of
+// cp.async.bulk (TMA) copies, in program order, as far ahead as the ring allows.
+//
+// What the ncu source page of the first design (decoder_sm100.cuh) showed: no hot spot, 3.1 G warp instructions,
+// ~2200 per warp and projection phase, almost all of it address arithmetic, predicates and staging around 24 MMAs,
+// executed by 2 warps per scheduler with nothing to hide fixed latencies behind (stall_wait 23 %, barrier 21 %,
+// long scoreboard 20 %). The phases were instruction- and latency-bound, 10-17 us each. Here:
+//   * weights are re-laid at engine creation in the exact order a warp consumes them (pack kernels below), with the
+//     LayerNorm gain folded into the weight columns and the LayerNorm bias folded into the projection bias, so a
+//     consumer warp's inner loop is LDS.128 (weights, ring) + 2 x LDS.128 (activations) + 2 x mma.sync, rolled;
+//   * a warp owns whole 8-column output groups: accumulators never leave registers, no cross-warp reduction, the
+//     epilogue (bias, residual, GELU, KV-cache scatter, or the fused (max, last index) of whisper.cpp:346-361) is
+//     applied to the mma fragment directly;
+//   * the producer is decoupled from the consumers' cluster barrier (an mbarrier in every CTA's shared memory that
+//     the 16 CTAs arrive on remotely through DSMEM), so the next phases' weights and the next layer's K/V are in
+//     flight while the current phase waits on its peers.
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "decoder_sm100.cuh"  // shared small helpers (mma wrapper, bf16 unpack, ex2, globaltimer, cluster ids)
+
+namespace wt {
+
+constexpr int kDsConsWarps = 8;
+constexpr int kDsConsThreads = kDsConsWarps * 32;
+constexpr int kDsThreads = kDsConsThreads + 32;  // + the producer warp
+constexpr int kDsRows = 16;                      // clips per cluster = rows of the one m16 MMA tile
+constexpr int kDsStageBytes = 32768;             // ring stage: one K/V chunk (128 keys) or <= 8 warps x upw weight units
+constexpr int kDsMaxStages = 6;
+constexpr int kDsMaxSeg = 31;
+constexpr int kDsMaxLayers = 12;
+constexpr int kDsUnitBytes = 512;                // one (8-column group, 32-wide k block) weight unit: 32 lanes x 16 B
+
+enum : int { DS_QKV = 0, DS_OUT = 1, DS_XQ = 2, DS_XOUT = 3, DS_FC1 = 4, DS_FC2 = 5, DS_LOGITS = 6, DS_NKIND = 7 };
+
+struct __align__(128) DsLayerDev {
+  const uint4* w[6];          // packed weight streams, DS_QKV .. DS_FC2 (whole matrix, CTA-slice-major)
+  const float* b[6];          // biases with the LayerNorm bias folded in
+  const __nv_bfloat16* kvx;   // cross-attention K/V stream: [B][H][chunk][K rows | V rows]
+  __nv_bfloat16 *kc, *vc;     // [B][H][32][64] self-attention cache
+};
+
+struct DsParams {
+  const DsLayerDev* layers;
+  int n_layers, n_clips, clip0, d, H, S, V;
+  int group_clips;
+  int rank, G;                    // filled in by the kernel
+  int upw;                        // weight units per warp and ring stage (6 for d = 384 / 768, 8 for d = 512)
+  int n_stages;                   // ring depth (host: what fits next to the activation tile)
+  int debug;
+  const uint4* w_logits;          // packed tied embedding (final LayerNorm gain folded in)
+  const float* b_logits;          // [V] tok_emb . lnf_beta
+  const __nv_bfloat16* tok_emb;   // [V][d] (embedding lookups)
+  const __nv_bfloat16* pos_emb;
+  int* tokens;                    // [B][32]
+  int* lens;
+  int* done;
+  int prompt_len, max_total, eot;
+  float* x;                       // [rows][d] residual stream
+  float* qs;                      // [rows][d] self-attention query
+  float* att;                     // [rows][d] self-attention output
+  float* qx;                      // [rows][d] cross-attention query
+  __nv_bfloat16* hmid;            // [rows][4d]
+  float* xpart;                   // [pairs][xslots][66]
+  int xslots;
+  unsigned long long* amax_part;  // [rows][kDecMaxCluster]
+  float* step_logits;
+  long long step_logits_stride;
+  int* finished;
+  unsigned long long* trace;
+};
+
+// per-CTA description of its stream (shared memory, built once by thread 0)
+struct DsStream {
+  long long slice_unit0[DS_NKIND];  // first weight unit of this CTA's slice, per kind
+  int ng[DS_NKIND];                 // 8-column groups owned by this CTA
+  int kph[DS_NKIND];                // ring stages per group = (K / 32) / upw
+  int nseg, nchunks, per, cpp;      // cross-attention range (as in decoder_sm100.cuh)
+  volatile int stop;                // consumers -> producer: leave after draining
+  volatile unsigned consumed;       // ring stages consumed when `stop` was raised
+};
+
+struct DsSmem {
+  static constexpr int kParams = 0;                                   // DsParams (<= 512 B)
+  static constexpr int kStream = 512;                                 // DsStream (<= 256 B)
+  static constexpr int kBars = 768;                                   // full[6] empty[6] cbar
+  static constexpr int kSegs = 896;                                   // int4[32]
+  static constexpr int kLayers = kSegs + 16 * 32;                     // DsLayerDev[12]
+  static constexpr int kMisc = kLayers + kDsMaxLayers * 128;          // cross-attn merge scratch: m[8] l[8] acc[8][64]
+  static constexpr int kBest = kMisc + (16 + 8 * 64) * 4;             // u64[16] argmax scratch
+  static constexpr int kXq = kBest + 16 * 8;                          // staged queries [kDsMaxSeg][64] f32
+  static constexpr int kA = (kXq + kDsMaxSeg * 64 * 4 + 127) & ~127;  // activation tile [16][4d] bf16 (+64 B per row)
+  __host__ __device__ static constexpr int a_stride(int d) { return 8 * d + 64; }
+  __host__ __device__ static constexpr int ring(int d) { return (kA + kDsRows * a_stride(d) + 1023) & ~1023; }
+  __host__ __device__ static constexpr int total(int d, int n_stages) { return ring(d) + n_stages * kDsStageBytes; }
+};
+
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred P1;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, P1;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void ds_cons_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kDsConsThreads) : "memory"); }
+__device__ __forceinline__ uint64_t l2_evict_last_policy() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+
+__device__ __forceinline__ uint64_t* ds_full(uint8_t* smem) { return reinterpret_cast<uint64_t*>(smem + DsSmem::kBars); }
+__device__ __forceinline__ uint64_t* ds_empty(uint8_t* smem) { return ds_full(smem) + kDsMaxStages; }
+__device__ __forceinline__ uint64_t* ds_cbar(uint8_t* smem) { return ds_full(smem) + 2 * kDsMaxStages; }
+__device__ __forceinline__ DsStream* ds_stream(uint8_t* smem) { return reinterpret_cast<DsStream*>(smem + DsSmem::kStream); }
+__device__ __forceinline__ int4* ds_segs(uint8_t* smem) { return reinterpret_cast<int4*>(smem + DsSmem::kSegs); }
+
+// Cluster-wide barrier of the CONSUMER warps: CTA-level named barrier, then one remote arrive per peer (lane i of
+// warp 0 -> CTA i's mbarrier, release at cluster scope — cumulative over the CTA's writes ordered by the named
+// barrier), then every consumer thread waits for its own CTA's mbarrier phase (acquire at cluster scope). Data other
+// CTAs wrote to global memory is read afterwards with L1-bypassing loads (__ldcg).
+__device__ __forceinline__ void ds_cluster_sync(uint8_t* smem, const DsParams& p, unsigned& cphase, int kind,
+                                                unsigned long long& tlast) {
+  const bool tr = p.trace != nullptr && threadIdx.x == 0;
+  const unsigned long long t_arr = tr ? dec_globaltimer() : 0ull;
+  ds_cons_bar();
+  const uint32_t local = smem_u32(ds_cbar(smem));
+  if (threadIdx.x < (unsigned)p.G) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(threadIdx.x));
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+  }
+  asm volatile(
+      "{\n\t.reg .pred P1;\n\t"
+      "DS_CW_LOOP:\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P1, [%0], %1;\n\t"
+      "@P1 bra DS_CW_DONE;\n\t"
+      "bra DS_CW_LOOP;\n\t"
+      "DS_CW_DONE:\n\t}" ::"r"(local),
+      "r"(cphase)
+      : "memory");
+  cphase ^= 1u;
+  if (tr) {
+    const unsigned long long t = dec_globaltimer();
+    atomicAdd(p.trace + kind, t - tlast);
+    atomicAdd(p.trace + 16 + kind, t - t_arr);
+    tlast = t;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Weight packing (engine creation). A "unit" is the 512 bytes one warp feeds to two m16n8k16 MMAs: for 8-column
+// group g and 32-wide k block kb, lane (gq = lane / 4, t = lane % 4) holds W[g*8 + gq][kb*32 + t*8 .. +8) — the K
+// permutation inside a k block is the one the activation fragments use (dec_mma_w in decoder_sm100.cuh). Units are
+// ordered the way the stream delivers them: CTA slice (gpc groups) -> round of 8 groups (one per consumer warp) ->
+// k phase (upw k blocks) -> warp -> unit, so a ring stage is one contiguous copy and warp w's share of it sits at
+// w * upw * 512.
+// ---------------------------------------------------------------------------------------------------
+__global__ void ds_pack_weights_kernel(const __nv_bfloat16* __restrict__ W, const float* __restrict__ gamma,
+                                       uint4* __restrict__ out, int N, int K, int G, int upw) {
+  const int n_groups = (N + 7) >> 3, kbK = K >> 5, gpc = (n_groups + G - 1) / G;
+  const long long total = (long long)n_groups * kbK * 32;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int lane = (int)(idx & 31);
+    const long long gk = idx >> 5;
+    const int kb = (int)(gk % kbK), g = (int)(gk / kbK);
+    const int r = g / gpc, gl = g - r * gpc;
+    const int ng_r = (n_groups - r * gpc < gpc) ? n_groups - r * gpc : gpc;
+    const int rho = gl >> 3, w = gl & 7;
+    const int nact = (ng_r - 8 * rho < 8) ? ng_r - 8 * rho : 8;
+    const int h = kb / upw, u = kb - h * upw;
+    const long long unit = (long long)r * gpc * kbK + (long long)rho * 8 * kbK + (long long)h * nact * upw + w * upw + u;
+    const int n = g * 8 + (lane >> 2), k0 = kb * 32 + (lane & 3) * 8;
+    uint32_t o[4] = {0u, 0u, 0u, 0u};
+    if (n < N) {
+      float f[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        f[j] = __bfloat162float(W[(size_t)n * K + k0 + j]);
+        if (gamma) f[j] *= gamma[k0 + j];
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) o[j] = dec_pack2(f[2 * j], f[2 * j + 1]);
+    }
+    out[unit * 32 + lane] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+// b'[n] = b[n] + sum_k W[n][k] * beta[k]   (one warp per output; b and/or beta may be null)
+__global__ void ds_fold_bias_kernel(const __nv_bfloat16* __restrict__ W, const float* __restrict__ b,
+                                    const float* __restrict__ beta, float* __restrict__ out, int N, int K) {
+  const int warp = (int)((blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (warp >= N) return;
+  float s = 0.0f;
+  if (beta)
+    for (int k = lane; k < K; k += 32) s = fmaf(__bfloat162float(W[(size_t)warp * K + k]), beta[k], s);
+  s = warp_sum(s);
+  if (lane == 0) out[warp] = s + (b ? b[warp] : 0.0f);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Activation tile: rows_pad = 16 rows x K bf16 in shared memory, row stride `as` bytes (== 64 mod 128, so the 16-byte
+// fragment loads of a quarter warp — 2 rows x 4 k pieces — cover all 32 banks once).
+// ---------------------------------------------------------------------------------------------------
+// LayerNorm without gain/bias (both folded into the packed weights): one warp per row, the row in registers
+__device__ __forceinline__ void ds_stage_norm(uint8_t* sA, int as, const float* x, int n_clips, int d) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int per = d >> 7;  // float4 per lane (d multiple of 128) — d = 64 handled by the tail path below
+  for (int r = warp; r < kDsRows; r += kDsConsWarps) {
+    uint8_t* dst = sA + (size_t)r * as;
+    if (r < n_clips && per > 0) {
+      float4 v[kDecMaxD / 128];
+      float s = 0.0f;
+#pragma unroll
+      for (int i = 0; i < kDecMaxD / 128; ++i)
+        if (i < per) {
+          v[i] = __ldcg(reinterpret_cast<const float4*>(x + (size_t)r * d + i * 128 + 4 * lane));
+          s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+        }
+      const float mean = warp_sum(s) / (float)d;
+      float q = 0.0f;
+#pragma unroll
+      for (int i = 0; i < kDecMaxD / 128; ++i)
+        if (i < per) {
+          v[i].x -= mean; v[i].y -= mean; v[i].z -= mean; v[i].w -= mean;
+          q += (v[i].x * v[i].x + v[i].y * v[i].y) + (v[i].z * v[i].z + v[i].w * v[i].w);
+        }
+      const float rstd = rsqrtf(warp_sum(q) / (float)d + 1e-5f);
+#pragma unroll
+      for (int i = 0; i < kDecMaxD / 128; ++i)
+        if (i < per)
+          *reinterpret_cast<uint2*>(dst + (i * 128 + 4 * lane) * 2) =
+              make_uint2(dec_pack2(v[i].x * rstd, v[i].y * rstd), dec_pack2(v[i].z * rstd, v[i].w * rstd));
+    } else if (r < n_clips) {
+      // d not a multiple of 128 (test-sized models): two elements per lane and pass
+      float s = 0.0f;
+      for (int c = 2 * lane; c < d; c += 64) {
+        const float2 t = __ldcg(reinterpret_cast<const float2*>(x + (size_t)r * d + c));
+        s += t.x + t.y;
+      }
+      const float mean = warp_sum(s) / (float)d;
+      float q = 0.0f;
+      for (int c = 2 * lane; c < d; c += 64) {
+        const float2 t = __ldcg(reinterpret_cast<const float2*>(x + (size_t)r * d + c));
+        q += (t.x - mean) * (t.x - mean) + (t.y - mean) * (t.y - mean);
+      }
+      const float rstd = rsqrtf(warp_sum(q) / (float)d + 1e-5f);
+      for (int c = 2 * lane; c < d; c += 64) {
+        const float2 t = __ldcg(reinterpret_cast<const float2*>(x + (size_t)r * d + c));
+        *reinterpret_cast<uint32_t*>(dst + c * 2) = dec_pack2((t.x - mean) * rstd, (t.y - mean) * rstd);
+      }
+    } else {
+      for (int c = lane; c < (d >> 1); c += 32) reinterpret_cast<uint32_t*>(dst)[c] = 0u;
+    }
+  }
+}
+__device__ __forceinline__ void ds_stage_f32(uint8_t* sA, int as, const float* src, int n_clips, int d) {
+  const int per_row = d >> 2;
+  for (int i = threadIdx.x; i < kDsRows * per_row; i += kDsConsThreads) {
+    const int r = i / per_row, c = (i - r * per_row) * 4;
+    uint2 o = make_uint2(0u, 0u);
+    if (r < n_clips) {
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(src + (size_t)r * d + c));
+      o = make_uint2(dec_pack2(v.x, v.y), dec_pack2(v.z, v.w));
+    }
+    *reinterpret_cast<uint2*>(sA + (size_t)r * as + c * 2) = o;
+  }
+}
+__device__ __forceinline__ void ds_stage_bf16(uint8_t* sA, int as, const __nv_bfloat16* src, int n_clips, int K) {
+  const int per_row = K >> 3;
+  for (int i = threadIdx.x; i < kDsRows * per_row; i += kDsConsThreads) {
+    const int r = i / per_row, c = (i - r * per_row) * 8;
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    if (r < n_clips) o = __ldcg(reinterpret_cast<const uint4*>(src + (size_t)r * K + c));
+    *reinterpret_cast<uint4*>(sA + (size_t)r * as + c * 2) = o;
+  }
+}
+// cross-attention output = softmax-merge of the per-CTA partials (acc[64], max, sum) of every CTA covering the pair
+__device__ __forceinline__ void ds_stage_xmerge(uint8_t* sA, int as, const DsParams& p, int per, int cpp, int n_clips,
+                                                int d) {
+  const int half = d >> 1;
+  for (int i = threadIdx.x; i < kDsRows * half; i += kDsConsThreads) {
+    const int r = i / half, c = (i - r * half) * 2;
+    uint32_t o = 0u;
+    if (r < n_clips) {
+      const int pr = r * p.H + (c >> 6), e = c & 63;
+      const int first = (pr * cpp) / per, last = ((pr + 1) * cpp - 1) / per;
+      const float* p0 = p.xpart + (size_t)pr * p.xslots * 66;
+      float M = -1.0e30f;
+      for (int k = 0; k <= last - first; ++k) M = fmaxf(M, __ldcg(p0 + k * 66 + 64));
+      float Lw = 0.0f, o0 = 0.0f, o1 = 0.0f;
+      for (int k = 0; k <= last - first; ++k) {
+        const float s1 = dec_ex2(__ldcg(p0 + k * 66 + 64) - M);
+        const float2 a2 = __ldcg(reinterpret_cast<const float2*>(p0 + k * 66 + e));
+        Lw = fmaf(__ldcg(p0 + k * 66 + 65), s1, Lw);
+        o0 = fmaf(a2.x, s1, o0);
+        o1 = fmaf(a2.y, s1, o1);
+      }
+      const float inv = 1.0f / Lw;
+      o = dec_pack2(o0 * inv, o1 * inv);
+    }
+    *reinterpret_cast<uint32_t*>(sA + (size_t)r * as + c * 2) = o;
+  }
+}
+
+// ring position of the consumers (uniform over the consumer threads)
+struct DsRing {
+  unsigned cons;  // stages consumed so far
+  int slot;
+  unsigned par;
+  __device__ __forceinline__ void advance(int n_stages) {
+    ++cons;
+    if (++slot == n_stages) { slot = 0; par ^= 1u; }
+  }
+};
+
+// One 8-column group per warp and round, accumulated over kph ring stages of upw units (2 MMAs each, two independent
+// accumulator chains). Returns with the warp's 16 x 8 tile in acc (rows g / g+8, columns 2t, 2t+1 of the group).
+__device__ __forceinline__ void ds_mma_round(uint8_t* smem, const DsParams& p, DsRing& rg, const uint8_t* ring,
+                                             const uint8_t* a_lane, int as, int kph, bool active, float (&acc)[4]) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int upw = p.upw;
+  uint64_t* full = ds_full(smem);
+  uint64_t* empty = ds_empty(smem);
+  float a0[4] = {0.0f, 0.0f, 0.0f, 0.0f}, a1[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+  for (int h = 0; h < kph; ++h) {
+    mbar_wait(full + rg.slot, rg.par);
+    if (active) {
+      const uint8_t* wp = ring + (size_t)rg.slot * kDsStageBytes + (size_t)(warp * upw) * kDsUnitBytes + lane * 16;
+      const uint8_t* ap = a_lane + (size_t)(h * upw) * 64;
+#pragma unroll 2
+      for (int u = 0; u < upw; ++u) {
+        const uint4 w = *reinterpret_cast<const uint4*>(wp + u * kDsUnitBytes);
+        const uint4 lo = *reinterpret_cast<const uint4*>(ap + u * 64);
+        const uint4 hi = *reinterpret_cast<const uint4*>(ap + u * 64 + 8 * as);
+        mma_bf16_16816(a0, lo.x, hi.x, lo.y, hi.y, w.x, w.y);
+        mma_bf16_16816(a1, lo.z, hi.z, lo.w, hi.w, w.z, w.w);
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty + rg.slot);
+    rg.advance(p.n_stages);
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) acc[j] = a0[j] + a1[j];
+}
+
+// ---- projections: stage the activation tile, then rounds of (MMA over the ring, epilogue on the fragment) ----
+__device__ __noinline__ void ds_gemm(uint8_t* smem, const DsParams& p, DsRing& rg, int kind, int l, int pos) {
+  const DsLayerDev& L = p.layers[l];
+  const DsStream* st = ds_stream(smem);
+  const int d = p.d, B = p.n_clips, as = DsSmem::a_stride(d);
+  uint8_t* sA = smem + DsSmem::kA;
+  switch (kind) {
+    case DS_OUT: ds_stage_f32(sA, as, p.att, B, d); break;
+    case DS_XOUT: ds_stage_xmerge(sA, as, p, st->per, st->cpp, B, d); break;
+    case DS_FC2: ds_stage_bf16(sA, as, p.hmid, B, 4 * d); break;
+    default: ds_stage_norm(sA, as, p.x, B, d); break;  // QKV, XQ, FC1: LayerNorm (gain/bias folded into W, b)
+  }
+  ds_cons_bar();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int ng = st->ng[kind], kph = st->kph[kind];
+  const int g0 = (int)(st->slice_unit0[kind] / (kph * p.upw));  // first group of this CTA's slice
+  const float* bias = L.b[kind];
+  const uint8_t* ring = smem + DsSmem::ring(d);
+  const uint8_t* a_lane = sA + (size_t)g * as + t * 16;
+  const bool resid = kind == DS_OUT || kind == DS_XOUT || kind == DS_FC2;
+  const bool r0 = g < B, r1 = g + 8 < B;
+  for (int rho = 0; rho * 8 < ng; ++rho) {
+    const bool active = rho * 8 + warp < ng;
+    const int n = (g0 + rho * 8 + warp) * 8 + 2 * t;  // this lane's first column
+    float2 bz = make_float2(0.0f, 0.0f), x0 = bz, x1 = bz;
+    if (active) {
+      bz = __ldg(reinterpret_cast<const float2*>(bias + n));
+      if (resid) {
+        if (r0) x0 = __ldcg(reinterpret_cast<const float2*>(p.x + (size_t)g * d + n));
+        if (r1) x1 = __ldcg(reinterpret_cast<const float2*>(p.x + (size_t)(g + 8) * d + n));
+      }
+    }
+    float acc[4];
+    ds_mma_round(smem, p, rg, ring, a_lane, as, kph, active, acc);
+    if (!active) continue;
+    const float v00 = acc[0] + bz.x, v01 = acc[1] + bz.y, v10 = acc[2] + bz.x, v11 = acc[3] + bz.y;
+    switch (kind) {
+      case DS_QKV:
+        if (n < d) {
+          if (r0) *reinterpret_cast<float2*>(p.qs + (size_t)g * d + n) = make_float2(v00, v01);
+          if (r1) *reinterpret_cast<float2*>(p.qs + (size_t)(g + 8) * d + n) = make_float2(v10, v11);
+        } else {
+          const int nn = n - d, isv = nn >= d, c = isv ? nn - d : nn;
+          __nv_bfloat16* cache = isv ? L.vc : L.kc;
+          const size_t col = (size_t)pos * 64 + (c & 63), hh = c >> 6;
+          if (r0) *reinterpret_cast<uint32_t*>(cache + ((size_t)(p.clip0 + g) * p.H + hh) * 32 * 64 + col) = dec_pack2(v00, v01);
+          if (r1) *reinterpret_cast<uint32_t*>(cache + ((size_t)(p.clip0 + g + 8) * p.H + hh) * 32 * 64 + col) = dec_pack2(v10, v11);
+        }
+        break;
+      case DS_XQ:
+        if (r0) *reinterpret_cast<float2*>(p.qx + (size_t)g * d + n) = make_float2(v00, v01);
+        if (r1) *reinterpret_cast<float2*>(p.qx + (size_t)(g + 8) * d + n) = make_float2(v10, v11);
+        break;
+      case DS_FC1:
+        if (r0) *reinterpret_cast<uint32_t*>(p.hmid + (size_t)g * 4 * d + n) = dec_pack2(gelu_erf(v00), gelu_erf(v01));
+        if (r1) *reinterpret_cast<uint32_t*>(p.hmid + (size_t)(g + 8) * 4 * d + n) = dec_pack2(gelu_erf(v10), gelu_erf(v11));
+        break;
+      default:  // residual update
+        if (r0) *reinterpret_cast<float2*>(p.x + (size_t)g * d + n) = make_float2(x0.x + v00, x0.y + v01);
+        if (r1) *reinterpret_cast<float2*>(p.x + (size_t)(g + 8) * d + n) = make_float2(x1.x + v10, x1.y + v11);
+        break;
+    }
+  }
+}
+
+// ---- final LayerNorm -> tied logits with a fused (max, last index) per row (whisper.cpp:346-361's tie rule) ----
+__device__ __noinline__ void ds_logits(uint8_t* smem, const DsParams& p, DsRing& rg, int pos) {
+  const DsStream* st = ds_stream(smem);
+  const int d = p.d, B = p.n_clips, V = p.V, as = DsSmem::a_stride(d);
+  uint8_t* sA = smem + DsSmem::kA;
+  unsigned long long* s_best = reinterpret_cast<unsigned long long*>(smem + DsSmem::kBest);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  if (tid < kDsRows) s_best[tid] = 0ull;
+  ds_stage_norm(sA, as, p.x, B, d);
+  ds_cons_bar();
+  const int ng = st->ng[DS_LOGITS], kph = st->kph[DS_LOGITS];
+  const int g0 = (int)(st->slice_unit0[DS_LOGITS] / (kph * p.upw));
+  const uint8_t* ring = smem + DsSmem::ring(d);
+  const uint8_t* a_lane = sA + (size_t)g * as + t * 16;
+  const int step = pos - (p.prompt_len - 1);
+  float* lg = p.step_logits ? p.step_logits + (size_t)step * p.step_logits_stride : nullptr;
+  const bool r0 = g < B, r1 = g + 8 < B;
+  unsigned long long best0 = 0ull, best1 = 0ull;
+  for (int rho = 0; rho * 8 < ng; ++rho) {
+    const bool active = rho * 8 + warp < ng;
+    const int n = (g0 + rho * 8 + warp) * 8 + 2 * t;
+    float2 bz = make_float2(0.0f, 0.0f);
+    if (active) bz = __ldg(reinterpret_cast<const float2*>(p.b_logits + n));  // padded to a multiple of 8 on the host
+    float acc[4];
+    ds_mma_round(smem, p, rg, ring, a_lane, as, kph, active, acc);
+    if (!active) continue;
+    const float v00 = acc[0] + bz.x, v01 = acc[1] + bz.y, v10 = acc[2] + bz.x, v11 = acc[3] + bz.y;
+    if (n < V) {
+      if (r0) best0 = u64_max(best0, pack_val_idx(v00, (unsigned)n));
+      if (r1) best1 = u64_max(best1, pack_val_idx(v10, (unsigned)n));
+    }
+    if (n + 1 < V) {
+      if (r0) best0 = u64_max(best0, pack_val_idx(v01, (unsigned)(n + 1)));
+      if (r1) best1 = u64_max(best1, pack_val_idx(v11, (unsigned)(n + 1)));
+    }
+    if (lg) {
+      if (r0) {
+        float* row = lg + (size_t)(p.clip0 + g) * V;
+        if (n < V) row[n] = v00;
+        if (n + 1 < V) row[n + 1] = v01;
+      }
+      if (r1) {
+        float* row = lg + (size_t)(p.clip0 + g + 8) * V;
+        if (n < V) row[n] = v10;
+        if (n + 1 < V) row[n + 1] = v11;
+      }
+    }
+  }
+  best0 = u64_max(best0, __shfl_xor_sync(0xffffffffu, best0, 1));
+  best0 = u64_max(best0, __shfl_xor_sync(0xffffffffu, best0, 2));
+  best1 = u64_max(best1, __shfl_xor_sync(0xffffffffu, best1, 1));
+  best1 = u64_max(best1, __shfl_xor_sync(0xffffffffu, best1, 2));
+  if (t == 0) {
+    if (best0 != 0ull) atomicMax(s_best + g, best0);
+    if (best1 != 0ull) atomicMax(s_best + g + 8, best1);
+  }
+  ds_cons_bar();
+  if (tid < B) p.amax_part[(size_t)tid * kDecMaxCluster + p.rank] = s_best[tid];
+}
+
+// ---- self-attention over cache rows 0..pos: one warp per (clip, head), lane = key ----
+__device__ __noinline__ void ds_self_attn(uint8_t* smem, const DsParams& p, const DsLayerDev& L, int pos) {
+  float* s_misc = reinterpret_cast<float*>(smem + DsSmem::kMisc);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int d = p.d, H = p.H, B = p.n_clips;
+  float* sq = s_misc + 16 + warp * 64;
+  for (int pr = p.rank * kDsConsWarps + warp; pr < B * H; pr += p.G * kDsConsWarps) {
+    const int b = pr / H, h = pr - b * H;
+    const size_t base = ((size_t)(p.clip0 + b) * H + h) * 32 * 64;
+    uint4 kr[8];
+    uint32_t vv[32];
+    {
+      // rows > pos of the cache hold stale (finite) data: loaded unconditionally, masked out of the softmax below
+      const uint4* kp = reinterpret_cast<const uint4*>(L.kc + base + (size_t)lane * 64);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) kr[i] = __ldcg(kp + i);
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j) vv[j] = __ldcg(reinterpret_cast<const uint32_t*>(L.vc + base + (size_t)j * 64 + 2 * lane));
+    const float2 q2 = __ldcg(reinterpret_cast<const float2*>(p.qs + (size_t)b * d + h * 64 + 2 * lane));
+    sq[2 * lane] = q2.x * 0.125f;
+    sq[2 * lane + 1] = q2.y * 0.125f;
+    __syncwarp();
+    float s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float kf[8];
+      bf16x8_to_f32(kr[i], kf);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s = fmaf(sq[i * 8 + j], kf[j], s);
+    }
+    if (lane > pos) s = -3.0e38f;
+    const float m = warp_max(s);
+    const float pw = (lane <= pos) ? __expf(s - m) : 0.0f;
+    const float lsum = warp_sum(pw);
+    float o0 = 0.0f, o1 = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const float pj = __shfl_sync(0xffffffffu, pw, j);
+      o0 = fmaf(pj, __uint_as_float(vv[j] << 16), o0);
+      o1 = fmaf(pj, __uint_as_float(vv[j] & 0xffff0000u), o1);
+    }
+    const float inv = 1.0f / lsum;
+    *reinterpret_cast<float2*>(p.att + (size_t)b * d + h * 64 + 2 * lane) = make_float2(o0 * inv, o1 * inv);
+    __syncwarp();
+  }
+}
+
+// ---- cross-attention: the group's (clip, head, chunk) space is cut into one contiguous range per CTA; the chunks of
+//      that range arrive through the ring in order. 8 lanes share a key (8 dims each), 4 keys per warp and load. ----
+__device__ __noinline__ void ds_cross_attn(uint8_t* smem, const DsParams& p, DsRing& rg) {
+  float* s_misc = reinterpret_cast<float*>(smem + DsSmem::kMisc);
+  float* s_q = reinterpret_cast<float*>(smem + DsSmem::kXq);
+  const uint8_t* ring = smem + DsSmem::ring(p.d);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int grp = lane >> 3, sub = lane & 7;
+  const int d = p.d, H = p.H, S = p.S;
+  const DsStream* st = ds_stream(smem);
+  const int4* segs = ds_segs(smem);
+  const int nseg = st->nseg, per = st->per, cpp = st->cpp;
+  uint64_t* full = ds_full(smem);
+  uint64_t* empty = ds_empty(smem);
+  float* sm_m = s_misc;             // [8]
+  float* sm_l = s_misc + 8;         // [8]
+  float* sm_acc = s_misc + 16;      // [8][64]
+  {
+    const float qscale = 0.125f * 1.4426950408889634f;
+    for (int i = tid; i < nseg * 64; i += kDsConsThreads) {
+      const int pr = segs[i >> 6].x, b = pr / H, h = pr - b * H;
+      s_q[i] = __ldcg(p.qx + (size_t)b * d + h * 64 + (i & 63)) * qscale;
+    }
+  }
+  ds_cons_bar();
+  for (int si = 0; si < nseg; ++si) {
+    const int4 sg = segs[si];  // {pair, first chunk, end chunk, ...}
+    const int pr = sg.x;
+    float qv[8];
+    {
+      const float4 q0 = *reinterpret_cast<const float4*>(s_q + si * 64 + sub * 8);
+      const float4 q1 = *reinterpret_cast<const float4*>(s_q + si * 64 + sub * 8 + 4);
+      qv[0] = q0.x; qv[1] = q0.y; qv[2] = q0.z; qv[3] = q0.w;
+      qv[4] = q1.x; qv[5] = q1.y; qv[6] = q1.z; qv[7] = q1.w;
+    }
+    float m = -1.0e30f, lsum = 0.0f, acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.0f;
+    for (int c = sg.y; c < sg.z; ++c) {
+      const int n_keys = (S - c * kXaChunk < kXaChunk) ? S - c * kXaChunk : kXaChunk;
+      mbar_wait(full + rg.slot, rg.par);
+      const uint8_t* stg = ring + (size_t)rg.slot * kDsStageBytes;
+      constexpr int kU = kXaChunk / (kDsConsWarps * 4);
+      uint4 kq[kU], vq[kU];
+      bool ok[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const int kl = u * (kDsConsWarps * 4) + warp * 4 + grp;
+        ok[u] = kl < n_keys;
+        kq[u] = *reinterpret_cast<const uint4*>(stg + (size_t)kl * 128 + sub * 16);
+        vq[u] = *reinterpret_cast<const uint4*>(stg + (size_t)(kXaChunk + kl) * 128 + sub * 16);
+        if (!ok[u]) {  // rows past the clip's last key are padding (never written): keep them out of the math
+          kq[u] = make_uint4(0u, 0u, 0u, 0u);
+          vq[u] = make_uint4(0u, 0u, 0u, 0u);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty + rg.slot);  // values are in registers: the producer may refill the stage
+      rg.advance(p.n_stages);
+      float sc[kU];
+      float mx = m;
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        float s = 0.0f;
+        float kf[8];
+        bf16x8_to_f32(kq[u], kf);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s = fmaf(qv[i], kf[i], s);
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        s += __shfl_xor_sync(0xffffffffu, s, 2);
+        s += __shfl_xor_sync(0xffffffffu, s, 4);
+        sc[u] = s;
+        if (ok[u]) mx = fmaxf(mx, s);
+      }
+      const float scale = dec_ex2(m - mx);
+      lsum *= scale;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] *= scale;
+      m = mx;
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        if (ok[u]) {
+          const float pw = dec_ex2(sc[u] - m);
+          lsum += pw;
+          float vf[8];
+          bf16x8_to_f32(vq[u], vf);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[i] = fmaf(pw, vf[i], acc[i]);
+        }
+      }
+    }
+    // merge the 4 key lanes of the warp (lanes with equal `sub` hold the same 8 dims)
+#pragma unroll
+    for (int o = 8; o <= 16; o <<= 1) {
+      const float m2 = __shfl_xor_sync(0xffffffffu, m, o);
+      const float l2 = __shfl_xor_sync(0xffffffffu, lsum, o);
+      const float mn = fmaxf(m, m2);
+      const float s1 = dec_ex2(m - mn), s2 = dec_ex2(m2 - mn);
+      lsum = lsum * s1 + l2 * s2;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float a2 = __shfl_xor_sync(0xffffffffu, acc[i], o);
+        acc[i] = acc[i] * s1 + a2 * s2;
+      }
+      m = mn;
+    }
+    ds_cons_bar();  // s_misc free (previous segment's merge done)
+    if (grp == 0) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) sm_acc[warp * 64 + sub * 8 + i] = acc[i];
+      if (sub == 0) {
+        sm_m[warp] = m;
+        sm_l[warp] = lsum;
+      }
+    }
+    ds_cons_bar();
+    // this CTA's partial (acc[64], max, sum) of pair `pr` goes to its slot; the out-projection's staging merges the
+    // slots of all CTAs that cover the pair after the cluster barrier
+    if (tid < 64) {
+      const int first_cta = (pr * cpp) / per;
+      float* pp = p.xpart + ((size_t)pr * p.xslots + (p.rank - first_cta)) * 66;
+      float M = sm_m[0];
+#pragma unroll
+      for (int w = 1; w < kDsConsWarps; ++w) M = fmaxf(M, sm_m[w]);
+      float Lw = 0.0f, O = 0.0f;
+#pragma unroll
+      for (int w = 0; w < kDsConsWarps; ++w) {
+        const float s1 = dec_ex2(sm_m[w] - M);
+        Lw = fmaf(sm_l[w], s1, Lw);
+        O = fmaf(sm_acc[w * 64 + tid], s1, O);
+      }
+      pp[tid] = O;
+      if (tid == 0) {
+        pp[64] = M;
+        pp[65] = Lw;
+      }
+    }
+  }
+}
+
+// ---- finalize (CTA b): append the winner, EOT bookkeeping ----
+__device__ __noinline__ void ds_finalize(uint8_t* smem, const DsParams& p, int pos) {
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int G = p.G;
+  // one warp per clip: lanes read the G per-CTA partial winners
+  for (int b = p.rank * kDsConsWarps + warp; b < p.n_clips; b += G * kDsConsWarps) {
+    unsigned long long v = 0ull;
+    if (lane < G) v = __ldcg(p.amax_part + (size_t)b * kDecMaxCluster + lane);
+    v = warp_max_u64(v);
+    if (lane == 0) {
+      const int tok = (int)(v & 0xffffffffull);
+      const int cb = p.clip0 + b;
+      if (!p.done[cb]) {
+        p.tokens[(size_t)cb * kDecTokStride + pos + 1] = tok;
+        p.lens[cb] = pos + 2;
+        if (tok == p.eot) {
+          p.done[cb] = 1;
+          atomicAdd(p.finished, 1);
+        }
+      }
+    }
+    __syncwarp();  // ds_embed (same warp, same clip) reads the token lane 0 just appended
+  }
+}
+
+// x[b] = tok_emb[token(b, pos)] + pos_emb[pos]   (a finished clip keeps stepping on its last token, unused)
+__device__ __noinline__ void ds_embed(const DsParams& p, int pos) {
+  const int d = p.d, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int b = p.rank * kDsConsWarps + warp; b < p.n_clips; b += p.G * kDsConsWarps) {
+    int tok = __ldcg(p.tokens + (size_t)(p.clip0 + b) * kDecTokStride + pos);
+    if (tok < 0) tok = 0;
+    const __nv_bfloat16* te = p.tok_emb + (size_t)tok * d;
+    const __nv_bfloat16* pe = p.pos_emb + (size_t)pos * d;
+    for (int c = 2 * lane; c < d; c += 64) {
+      const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(te + c);
+      const __nv_bfloat162 e = *reinterpret_cast<const __nv_bfloat162*>(pe + c);
+      *reinterpret_cast<float2*>(p.x + (size_t)b * d + c) =
+          make_float2(__bfloat162float(a.x) + __bfloat162float(e.x), __bfloat162float(a.y) + __bfloat162float(e.y));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Producer (one thread): walks the CTA's whole stream in program order — every source is constant for the launch
+// (packed weights, the K/V stream written by the encoder side), so it never depends on the consumers' data, only on
+// free ring stages. Returns the number of stages issued.
+// ---------------------------------------------------------------------------------------------------
+struct DsProd {
+  uint8_t* smem;
+  uint8_t* ring;
+  uint64_t *full, *empty;
+  DsStream* st;
+  unsigned n;
+  int slot, n_stages;
+  unsigned par;
+  __device__ __forceinline__ bool issue(const void* src, uint32_t bytes, uint64_t policy) {
+    while (!mbar_try_wait(empty + slot, par ^ 1u)) {
+      if (st->stop) return false;
+    }
+    mbar_expect_tx(full + slot, bytes);
+    bulk_load_stream(ring + (size_t)slot * kDsStageBytes, src, bytes, full + slot, policy);
+    ++n;
+    if (++slot == n_stages) { slot = 0; par ^= 1u; }
+    return true;
+  }
+  __device__ __forceinline__ bool weights(const uint4* base, int kind, int upw, uint64_t policy) {
+    const int ng = st->ng[kind], kph = st->kph[kind];
+    const uint4* src = base + st->slice_unit0[kind] * 32;
+    for (int rho = 0; rho * 8 < ng; ++rho) {
+      const int nact = (ng - rho * 8 < 8) ? ng - rho * 8 : 8;
+      const uint32_t bytes = (uint32_t)(nact * upw * kDsUnitBytes);
+      for (int h = 0; h < kph; ++h) {
+        if (!issue(src, bytes, policy)) return false;
+        src += bytes >> 4;
+      }
+    }
+    return true;
+  }
+};
+
+__device__ __noinline__ unsigned ds_producer(uint8_t* smem, const DsParams& p) {
+  DsProd pr;
+  pr.smem = smem;
+  pr.ring = smem + DsSmem::ring(p.d);
+  pr.full = ds_full(smem);
+  pr.empty = ds_empty(smem);
+  pr.st = ds_stream(smem);
+  pr.n = 0; pr.slot = 0; pr.par = 0; pr.n_stages = p.n_stages;
+  const uint64_t pol_kv = l2_evict_first_policy(), pol_w = l2_evict_last_policy();
+  const int4* segs = ds_segs(smem);
+  const int nseg = pr.st->nseg, cpp = pr.st->cpp, upw = p.upw;
+  const size_t chunk_elems = (size_t)2 * kXaChunk * 64;
+  for (int pos = 0; pos <= p.max_total - 2; ++pos) {
+    for (int l = 0; l < p.n_layers; ++l) {
+      const DsLayerDev& L = p.layers[l];
+      if (!pr.weights(L.w[DS_QKV], DS_QKV, upw, pol_w)) return pr.n;
+      if (!pr.weights(L.w[DS_OUT], DS_OUT, upw, pol_w)) return pr.n;
+      if (!pr.weights(L.w[DS_XQ], DS_XQ, upw, pol_w)) return pr.n;
+      for (int si = 0; si < nseg; ++si) {
+        const int4 sg = segs[si];
+        const __nv_bfloat16* src = L.kvx + (((size_t)p.clip0 * p.H + sg.x) * cpp + sg.y) * chunk_elems;
+        for (int c = sg.y; c < sg.z; ++c, src += chunk_elems)
+          if (!pr.issue(src, (uint32_t)kDsStageBytes, pol_kv)) return pr.n;
+      }
+      if (!pr.weights(L.w[DS_XOUT], DS_XOUT, upw, pol_w)) return pr.n;
+      if (!pr.weights(L.w[DS_FC1], DS_FC1, upw, pol_w)) return pr.n;
+      if (!pr.weights(L.w[DS_FC2], DS_FC2, upw, pol_w)) return pr.n;
+    }
+    if (pos >= p.prompt_len - 1)
+      if (!pr.weights(p.w_logits, DS_LOGITS, upw, pol_w)) return pr.n;
+  }
+  return pr.n;
+}
+
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsParams p_in) {
+  extern __shared__ __align__(1024) uint8_t ds_smem[];
+  const int tid = threadIdx.x, warp = tid >> 5;
+  DsParams& p = *reinterpret_cast<DsParams*>(ds_smem + DsSmem::kParams);
+  static_assert(sizeof(DsParams) <= 512, "DsParams outgrew its shared-memory slot");
+  static_assert(sizeof(DsStream) <= 256, "DsStream outgrew its shared-memory slot");
+  static_assert(sizeof(DsLayerDev) == 128, "DsLayerDev slot size");
+  const int G = (int)dec_cluster_nctarank();
+  const int rank = (int)dec_cluster_ctarank();
+  const int group = (int)dec_clusterid_x();
+  const int gc = p_in.group_clips;
+  const int first = group * gc;
+  const int nb = (p_in.n_clips - first < gc) ? p_in.n_clips - first : gc;
+  if (nb <= 0 || p_in.n_layers > kDsMaxLayers) return;  // whole cluster leaves together
+  if (tid == 0) {
+    p = p_in;
+    p.G = G;
+    p.rank = rank;
+    p.clip0 = p_in.clip0 + first;
+    p.n_clips = nb;
+    const size_t row0 = (size_t)group * kDsRows;
+    p.x += row0 * p.d;
+    p.qs += row0 * p.d;
+    p.att += row0 * p.d;
+    p.qx += row0 * p.d;
+    p.hmid += row0 * 4 * p.d;
+    p.xpart += row0 * p.H * (size_t)p.xslots * 66;
+    p.amax_part += row0 * kDecMaxCluster;
+    p.finished += group;
+    if (group != 0 || rank != 0) p.trace = nullptr;
+    p.layers = reinterpret_cast<const DsLayerDev*>(ds_smem + DsSmem::kLayers);
+    // ---- this CTA's stream: weight slices per kind, cross-attention range ----
+    DsStream* st = ds_stream(ds_smem);
+    const int d = p.d;
+    for (int k = 0; k < DS_NKIND; ++k) {
+      const int N = (k == DS_QKV) ? 3 * d : (k == DS_FC1) ? 4 * d : (k == DS_LOGITS) ? p.V : d;
+      const int kbK = ((k == DS_FC2) ? 4 * d : d) >> 5;
+      const int n_groups = (N + 7) >> 3, gpc = (n_groups + G - 1) / G;
+      int ng = n_groups - rank * gpc;
+      ng = ng < 0 ? 0 : (ng > gpc ? gpc : ng);
+      st->ng[k] = ng;
+      st->kph[k] = kbK / p.upw;
+      st->slice_unit0[k] = (long long)rank * gpc * kbK;
+    }
+    int4* segs = ds_segs(ds_smem);
+    const int cpp = (p.S + kXaChunk - 1) / kXaChunk;
+    const int T = nb * p.H * cpp;
+    const int per = (T + G - 1) / G;
+    int cur = rank * per;
+    const int hi = (cur + per < T) ? cur + per : T;
+    int nseg = 0, nchunks = 0;
+    while (cur < hi && nseg < kDsMaxSeg) {
+      const int pr = cur / cpp;
+      const int c0 = cur - pr * cpp;
+      const int c1 = (hi - cur < cpp - c0) ? c0 + (hi - cur) : cpp;
+      segs[nseg] = make_int4(pr, c0, c1, nchunks);
+      nchunks += c1 - c0;
+      ++nseg;
+      cur += c1 - c0;
+    }
+    st->nseg = nseg;
+    st->nchunks = nchunks;
+    st->per = per;
+    st->cpp = cpp;
+    st->stop = 0;
+    st->consumed = 0u;
+    for (int i = 0; i < kDsMaxStages; ++i) {
+      mbar_init(ds_full(ds_smem) + i, 1);
+      mbar_init(ds_empty(ds_smem) + i, kDsConsWarps);
+    }
+    mbar_init(ds_cbar(ds_smem), (uint32_t)G);
+    fence_barrier_init();
+  }
+  {
+    const int words = (int)(sizeof(DsLayerDev) / 8);
+    for (int i = tid; i < p_in.n_layers * words; i += kDsThreads)
+      reinterpret_cast<unsigned long long*>(ds_smem + DsSmem::kLayers)[i] =
+          reinterpret_cast<const unsigned long long*>(p_in.layers)[i];
+  }
+  __syncthreads();
+  // every CTA's barriers exist before any peer arrives on them
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+
+  unsigned issued = 0;
+  if (warp == kDsConsWarps) {
+    if (tid == kDsConsThreads) issued = ds_producer(ds_smem, p);
+  } else {
+    const int B = p.n_clips;
+    unsigned long long tlast = (p.trace != nullptr && tid == 0) ? dec_globaltimer() : 0ull;
+    unsigned cphase = 0;
+    DsRing rg;
+    rg.cons = 0; rg.slot = 0; rg.par = 0;
+    if (tid == 0) {
+      for (int b = rank; b < B; b += G) {
+        p.lens[p.clip0 + b] = p.prompt_len;
+        p.done[p.clip0 + b] = 0;
+      }
+    }
+    ds_embed(p, 0);
+    ds_cluster_sync(ds_smem, p, cphase, 0, tlast);
+    for (int pos = 0; pos <= p.max_total - 2; ++pos) {
+      for (int l = 0; l < p.n_layers; ++l) {
+        const DsLayerDev& L = p.layers[l];
+        ds_gemm(ds_smem, p, rg, DS_QKV, l, pos);    // 1. LN1 -> QKV; q -> qs, k/v -> cache row `pos`
+        ds_cluster_sync(ds_smem, p, cphase, 1, tlast);
+        ds_self_attn(ds_smem, p, L, pos);           // 2. self-attention over cache rows 0..pos
+        ds_cluster_sync(ds_smem, p, cphase, 2, tlast);
+        ds_gemm(ds_smem, p, rg, DS_OUT, l, pos);    // 3. out-proj + residual
+        ds_cluster_sync(ds_smem, p, cphase, 3, tlast);
+        ds_gemm(ds_smem, p, rg, DS_XQ, l, pos);     // 4. LNx -> cross-attention query
+        ds_cluster_sync(ds_smem, p, cphase, 4, tlast);
+        ds_cross_attn(ds_smem, p, rg);              // 5. cross-attention over this CTA's K/V range
+        ds_cluster_sync(ds_smem, p, cphase, 5, tlast);
+        ds_gemm(ds_smem, p, rg, DS_XOUT, l, pos);   // 6. merge of the partials -> out-proj + residual
+        ds_cluster_sync(ds_smem, p, cphase, 6, tlast);
+        ds_gemm(ds_smem, p, rg, DS_FC1, l, pos);    // 7. LN2 -> fc1 -> GELU
+        ds_cluster_sync(ds_smem, p, cphase, 7, tlast);
+        ds_gemm(ds_smem, p, rg, DS_FC2, l, pos);    // 8. fc2 + residual
+        ds_cluster_sync(ds_smem, p, cphase, 8, tlast);
+      }
+      if (pos >= p.prompt_len - 1) {
+        ds_logits(ds_smem, p, rg, pos);
+        ds_cluster_sync(ds_smem, p, cphase, 9, tlast);
+        ds_finalize(ds_smem, p, pos);
+      }
+      if (pos + 1 <= p.max_total - 2) ds_embed(p, pos + 1);
+      ds_cluster_sync(ds_smem, p, cphase, 10, tlast);
+      if (__ldcg(p.finished) >= B) break;  // every clip has produced EOT (whisper.cpp:397-399, per clip)
+    }
+    if (tid == 0) {
+      DsStream* st = ds_stream(ds_smem);
+      st->consumed = rg.cons;
+      __threadfence_block();
+      st->stop = 1;
+    }
+  }
+  __syncthreads();
+  // stages requested but never consumed (early EOT) must land before this CTA's shared memory goes away
+  if (tid == kDsConsThreads) {
+    const unsigned consumed = ds_stream(ds_smem)->consumed;
+    for (unsigned j = consumed; j < issued; ++j) mbar_wait(ds_full(ds_smem) + (j % p.n_stages), (j / p.n_stages) & 1u);
+  }
+  __syncthreads();
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+}  // namespace wt

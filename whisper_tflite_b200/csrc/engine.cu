@@ -24,6 +24,7 @@
 #include "../../include/whisper_b200.h"
 #include "attn_sm100.cuh"
 #include "decoder_sm100.cuh"
+#include "decoder_stream_sm100.cuh"
 #include "gemm_sm100.cuh"
 #include "mel_host.h"
 #include "mel_kernels.cuh"
@@ -279,6 +280,13 @@ struct wt_engine {
   int* pd_finished = nullptr;
   unsigned long long* pd_trace = nullptr;  // WT_DEC_TRACE=1: per-phase ns of the persistent decoder (CTA 0)
   int pd_xslots_cap = 0;
+  // streaming flavour (decoder_stream_sm100.cuh, the default): packed weight streams + one producer warp per CTA
+  bool dec_stream = false;
+  wt::DsLayerDev* d_ds_layers = nullptr;
+  uint4* ds_w_logits = nullptr;
+  float* ds_b_logits = nullptr;
+  int ds_upw = 0, ds_stages = 0, ds_smem = 0;
+  int init_stream_weights();
   int enc_clips = 0;  // clips whose encoder states / cross K,V are resident
   std::map<std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint64_t, uint64_t, uint32_t>, CUtensorMap> map_cache;
 
@@ -734,7 +742,28 @@ bool wt_engine::persistent_decoder_wanted() const {
 
 int wt_engine::init_persistent_decoder() {
   if (!persistent_decoder_wanted()) return WT_OK;
-  WT_CUDA_OK(cudaFuncSetAttribute(wt::decoder_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::DecSmem::kTotal));
+  {
+    const char* ov = getenv("WT_DECODER");
+    dec_stream = !(ov && strcmp(ov, "cluster") == 0);
+  }
+  const void* kfn = dec_stream ? (const void*)wt::decoder_stream_kernel : (const void*)wt::decoder_persistent_kernel;
+  const int kthreads = dec_stream ? wt::kDsThreads : wt::kDecThreads;
+  int ksmem = wt::DecSmem::kTotal;
+  if (dec_stream) {
+    const int kbK = dims.d_model / 32;
+    if (dims.d_model % 64 != 0) return fail(WT_ERR_INVALID, "streaming decoder needs d_model %% 64 == 0");
+    const int cand[6] = {8, 6, 4, 3, 2, 1};
+    for (int i = 0; i < 6 && !ds_upw; ++i)
+      if (kbK % cand[i] == 0) ds_upw = cand[i];
+    int max_optin = 0;
+    WT_CUDA_OK(cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    ds_stages = (max_optin - wt::DsSmem::ring(dims.d_model)) / wt::kDsStageBytes;
+    if (ds_stages > wt::kDsMaxStages) ds_stages = wt::kDsMaxStages;
+    if (const char* os = getenv("WT_DEC_STAGES")) ds_stages = atoi(os) < ds_stages ? atoi(os) : ds_stages;
+    if (ds_stages < 2) return fail(WT_ERR_INVALID, "streaming decoder: shared memory holds only %d ring stages at d_model %d", ds_stages, dims.d_model);
+    ksmem = ds_smem = wt::DsSmem::total(dims.d_model, ds_stages);
+  }
+  WT_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, ksmem));
   // cluster shape: 16 CTAs x 8 clips (8 clusters fill 128 SMs at B = 64) when the device can co-schedule a 16-CTA
   // cluster per GPC, else the portable 8 CTAs x 4 clips. WT_DEC_CLUSTER / WT_DEC_GROUP override (probing).
   dec_cluster = 0;
@@ -744,7 +773,7 @@ int wt_engine::init_persistent_decoder() {
     const int cs = ocl ? atoi(ocl) : want[i];
     if (cs < 1 || cs > wt::kDecMaxCluster) return fail(WT_ERR_INVALID, "WT_DEC_CLUSTER must be in [1, %d]", wt::kDecMaxCluster);
     if (cs > 8) {
-      if (cudaFuncSetAttribute(wt::decoder_persistent_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+      if (cudaFuncSetAttribute(kfn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
         cudaGetLastError();
         if (ocl) return fail(WT_ERR_CUDA, "cluster size %d is not allowed on this device", cs);
         continue;
@@ -752,15 +781,15 @@ int wt_engine::init_persistent_decoder() {
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(cs);
-    cfg.blockDim = dim3(wt::kDecThreads);
-    cfg.dynamicSmemBytes = wt::DecSmem::kTotal;
+    cfg.blockDim = dim3(kthreads);
+    cfg.dynamicSmemBytes = ksmem;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
     int n_active = 0;
-    if (cudaOccupancyMaxActiveClusters(&n_active, wt::decoder_persistent_kernel, &cfg) != cudaSuccess) { cudaGetLastError(); n_active = 0; }
+    if (cudaOccupancyMaxActiveClusters(&n_active, kfn, &cfg) != cudaSuccess) { cudaGetLastError(); n_active = 0; }
     if (n_active >= 1) { dec_cluster = cs; dec_active_clusters = n_active; }
     if (ocl) break;
   }
@@ -803,11 +832,59 @@ int wt_engine::init_persistent_decoder() {
   if (const char* tr = getenv("WT_DEC_TRACE")) {
     if (tr[0] == '1') {
       WT_TRY(alloc(&pd_trace, 32, true));
-      fprintf(stderr, "[whisper_b200] persistent decoder: cluster %d CTAs x %d clips, %d clusters co-resident, smem %d B\n",
-              dec_cluster, dec_group, dec_active_clusters, (int)wt::DecSmem::kTotal);
+      fprintf(stderr, "[whisper_b200] persistent decoder (%s): cluster %d CTAs x %d clips, %d clusters co-resident, smem %d B, ring %d stages, upw %d\n",
+              dec_stream ? "stream" : "cluster", dec_cluster, dec_group, dec_active_clusters, ksmem, ds_stages, ds_upw);
     }
   }
+  if (dec_stream) WT_TRY(init_stream_weights());
   dec_persistent = true;
+  return WT_OK;
+}
+
+// Packed weight streams of the streaming decoder: every projection re-laid in consumption order for this cluster size,
+// LayerNorm gains folded into the weight columns, LayerNorm biases into the projection biases.
+int wt_engine::init_stream_weights() {
+  const int d = dims.d_model, V = dims.n_vocab, G = dec_cluster;
+  std::vector<wt::DsLayerDev> hl(dims.n_dec_layers);
+  auto pack = [&](const Lin& lin, const LNp* ln, const uint4** w_out, const float** b_out) -> int {
+    const int n_groups = (lin.N + 7) / 8, kbK = lin.K / 32;
+    uint4* pw = nullptr;
+    float* pb = nullptr;
+    WT_TRY(alloc(&pw, (size_t)n_groups * kbK * 32));
+    WT_TRY(alloc(&pb, (size_t)n_groups * 8, true));
+    const long long total = (long long)n_groups * kbK * 32;
+    const int blocks = (int)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096);
+    wt::ds_pack_weights_kernel<<<blocks, 256, 0, stream>>>((const bf16*)lin.w, ln ? ln->g : nullptr, pw, lin.N, lin.K, G, ds_upw);
+    wt::ds_fold_bias_kernel<<<(lin.N * 32 + 255) / 256, 256, 0, stream>>>((const bf16*)lin.w, lin.b, ln ? ln->b : nullptr, pb, lin.N, lin.K);
+    WT_CUDA_OK(cudaGetLastError());
+    *w_out = pw;
+    *b_out = pb;
+    return WT_OK;
+  };
+  for (int i = 0; i < dims.n_dec_layers; ++i) {
+    DecLayer& L = dec[i];
+    wt::DsLayerDev& o = hl[i];
+    WT_TRY(pack(L.qkv, &L.ln1, &o.w[wt::DS_QKV], &o.b[wt::DS_QKV]));
+    WT_TRY(pack(L.out, nullptr, &o.w[wt::DS_OUT], &o.b[wt::DS_OUT]));
+    WT_TRY(pack(L.xq, &L.lnx, &o.w[wt::DS_XQ], &o.b[wt::DS_XQ]));
+    WT_TRY(pack(L.xout, nullptr, &o.w[wt::DS_XOUT], &o.b[wt::DS_XOUT]));
+    WT_TRY(pack(L.fc1, &L.ln2, &o.w[wt::DS_FC1], &o.b[wt::DS_FC1]));
+    WT_TRY(pack(L.fc2, nullptr, &o.w[wt::DS_FC2], &o.b[wt::DS_FC2]));
+    o.kvx = (const bf16*)L.kvx;
+    o.kc = (bf16*)L.kc; o.vc = (bf16*)L.vc;
+  }
+  {
+    Lin emb;
+    emb.w = tok_emb; emb.b = nullptr; emb.N = V; emb.K = d;
+    const uint4* w = nullptr;
+    const float* b = nullptr;
+    WT_TRY(pack(emb, &dec_ln, &w, &b));
+    ds_w_logits = const_cast<uint4*>(w);
+    ds_b_logits = const_cast<float*>(b);
+  }
+  WT_TRY(alloc(&d_ds_layers, hl.size()));
+  WT_CUDA_OK(cudaMemcpyAsync(d_ds_layers, hl.data(), hl.size() * sizeof(wt::DsLayerDev), cudaMemcpyHostToDevice, stream));
+  WT_CUDA_OK(cudaStreamSynchronize(stream));
   return WT_OK;
 }
 
@@ -821,6 +898,57 @@ int wt_engine::decode_persistent(int n_clips, int prompt_len, int max_total, int
   }
   const int n_groups = (n_clips + gsz - 1) / gsz;
   WT_CUDA_OK(cudaMemsetAsync(pd_finished, 0, (size_t)dec_groups_cap * sizeof(int), stream));
+  if (dec_stream) {
+    wt::DsParams q{};
+    q.layers = d_ds_layers;
+    q.n_layers = dims.n_dec_layers;
+    q.n_clips = n_clips;
+    q.clip0 = 0;
+    q.group_clips = gsz;
+    q.upw = ds_upw;
+    q.n_stages = ds_stages;
+    if (const char* dbg = getenv("WT_DEC_DEBUG")) q.debug = atoi(dbg);
+    q.d = d; q.H = H; q.S = S; q.V = dims.n_vocab;
+    q.w_logits = ds_w_logits; q.b_logits = ds_b_logits;
+    q.tok_emb = (const bf16*)tok_emb;
+    q.pos_emb = (const bf16*)dec_pos;
+    q.tokens = tokens; q.lens = lens; q.done = done;
+    q.prompt_len = prompt_len; q.max_total = max_total; q.eot = eot;
+    q.x = pd_x; q.qs = pd_qs; q.att = pd_att; q.qx = pd_qx; q.hmid = pd_hmid;
+    q.xpart = pd_xpart;
+    {
+      int slots = 0;
+      const int last = n_clips - (n_groups - 1) * gsz;
+      const int cand[2] = {n_groups > 1 ? gsz : last, last};
+      const int cpp = (S + wt::kXaChunk - 1) / wt::kXaChunk;
+      for (int i = 0; i < 2; ++i) {
+        const int per = (cand[i] * H * cpp + dec_cluster - 1) / dec_cluster;
+        const int sl = (cpp + per - 1) / per + 1;
+        if (sl > slots) slots = sl;
+      }
+      q.xslots = slots;
+    }
+    if (q.xslots > pd_xslots_cap) return fail(WT_ERR_STATE, "cross-attention partial slots %d exceed capacity %d", q.xslots, pd_xslots_cap);
+    q.amax_part = pd_amax;
+    q.step_logits = keep_logits ? step_logits : nullptr;
+    q.step_logits_stride = (long long)max_batch * dims.n_vocab;
+    q.finished = pd_finished;
+    q.trace = pd_trace;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(n_groups * dec_cluster);
+    cfg.blockDim = dim3(wt::kDsThreads);
+    cfg.dynamicSmemBytes = ds_smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = dec_cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    stage = ST_DEC_PERSISTENT;
+    pre_launch();
+    WT_CUDA_OK(cudaLaunchKernelEx(&cfg, wt::decoder_stream_kernel, q));
+    return check_launch("decoder_stream_kernel");
+  }
   WT_CUDA_OK(cudaMemsetAsync(pd_xtickets, 0, (size_t)dec_groups_cap * wt::kDecGroupMax * H * sizeof(unsigned), stream));
   wt::DecParams p{};
   p.layers = d_dec_layers;
