@@ -33,7 +33,7 @@ constexpr int kDsThreads = kDsConsThreads + 32;  // + the producer warp
 constexpr int kDsRows = 16;                      // clips per cluster = rows of the one m16 MMA tile
 constexpr int kDsStageBytes = 32768;             // ring stage: one K/V chunk (128 keys) or <= 8 warps x upw weight units
 constexpr int kDsMaxStages = 6;
-constexpr int kDsMaxSeg = 31;
+constexpr int kDsMaxSeg = 24;                     // (clip, head) pairs one CTA may own
 constexpr int kDsMaxLayers = 12;
 constexpr int kDsUnitBytes = 512;                // one (8-column group, 32-wide k block) weight unit: 32 lanes x 16 B
 
@@ -51,8 +51,8 @@ struct DsParams {
   int n_layers, n_clips, clip0, d, H, S, V;
   int group_clips;
   int rank, G;                    // filled in by the kernel
-  int upw;                        // weight units per warp and ring stage (6 for d = 384 / 768, 8 for d = 512)
-  int n_stages;                   // ring depth (host: what fits next to the activation tile)
+  int upw;                        // weight units per warp and ring stage (6 for d = 384, 8 for d = 512 / 768)
+  int n_stages;                   // ring depth (host: what fits next to the activation tiles)
   int debug;
   const uint4* w_logits;          // packed tied embedding (final LayerNorm gain folded in)
   const float* b_logits;          // [V] tok_emb . lnf_beta
@@ -62,17 +62,9 @@ struct DsParams {
   int* lens;
   int* done;
   int prompt_len, max_total, eot;
-  float* x;                       // [rows][d] residual stream
-  float* qs;                      // [rows][d] self-attention query
-  float* att;                     // [rows][d] self-attention output
-  float* qx;                      // [rows][d] cross-attention query
-  __nv_bfloat16* hmid;            // [rows][4d]
-  float* xpart;                   // [pairs][xslots][66]
-  int xslots;
-  unsigned long long* amax_part;  // [rows][kDecMaxCluster]
+  float* qs;                      // [rows][d] self-attention query (global: read together with the KV cache)
   float* step_logits;
   long long step_logits_stride;
-  int* finished;
   unsigned long long* trace;
 };
 
@@ -81,23 +73,33 @@ struct DsStream {
   long long slice_unit0[DS_NKIND];  // first weight unit of this CTA's slice, per kind
   int ng[DS_NKIND];                 // 8-column groups owned by this CTA
   int kph[DS_NKIND];                // ring stages per group = (K / 32) / upw
-  int nseg, nchunks, per, cpp;      // cross-attention range (as in decoder_sm100.cuh)
+  int pair0, npairs;                // cross-attention: whole (clip, head) pairs [pair0, pair0 + npairs) of the group
+  int pair_base, pair_rem;          // balanced split of the group's pairs over the cluster
+  int cpp;                          // K/V chunks per pair
   volatile int stop;                // consumers -> producer: leave after draining
   volatile unsigned consumed;       // ring stages consumed when `stop` was raised
 };
 
+// Shared memory. Activations never go through global memory between phases: every CTA holds a full copy of the
+// group's residual stream (sX, bf16, LayerNorm input), of the current K = d MMA operand (sA: LayerNorm output, or the
+// attention outputs its peers pushed) and of the MLP hidden state (sH), and producers of a slice push it into all
+// peers' copies with st.shared::cluster before the cluster barrier.
 struct DsSmem {
-  static constexpr int kParams = 0;                                   // DsParams (<= 512 B)
-  static constexpr int kStream = 512;                                 // DsStream (<= 256 B)
-  static constexpr int kBars = 768;                                   // full[6] empty[6] cbar
-  static constexpr int kSegs = 896;                                   // int4[32]
-  static constexpr int kLayers = kSegs + 16 * 32;                     // DsLayerDev[12]
-  static constexpr int kMisc = kLayers + kDsMaxLayers * 128;          // cross-attn merge scratch: m[8] l[8] acc[8][64]
-  static constexpr int kBest = kMisc + (16 + 8 * 64) * 4;             // u64[16] argmax scratch
-  static constexpr int kXq = kBest + 16 * 8;                          // staged queries [kDsMaxSeg][64] f32
-  static constexpr int kA = (kXq + kDsMaxSeg * 64 * 4 + 127) & ~127;  // activation tile [16][4d] bf16 (+64 B per row)
-  __host__ __device__ static constexpr int a_stride(int d) { return 8 * d + 64; }
-  __host__ __device__ static constexpr int ring(int d) { return (kA + kDsRows * a_stride(d) + 1023) & ~1023; }
+  static constexpr int kParams = 0;                                   // DsParams (<= 256 B)
+  static constexpr int kStream = 256;                                 // DsStream (<= 256 B)
+  static constexpr int kBars = 512;                                   // full[6] empty[6] cbar
+  static constexpr int kTok = 640;                                    // int[16] tokens of the step, int[16] done flags
+  static constexpr int kLayers = 768;                                 // DsLayerDev[12]
+  static constexpr int kMisc = kLayers + kDsMaxLayers * 128;          // merge scratch: m[8] l[8] acc[8][64] f32
+  static constexpr int kAmax = kMisc + (16 + 8 * 64) * 4;             // u64[16 ranks][16 rows] partial winners
+  static constexpr int kXq = kAmax + kDecMaxCluster * kDsRows * 8;    // queries of this CTA's pairs [kDsMaxSeg][64] f32
+  static constexpr int kX = kXq + kDsMaxSeg * 64 * 4;                 // sX
+  __host__ __device__ static constexpr int x_stride(int d) { return 2 * d; }
+  __host__ __device__ static constexpr int a_stride(int d) { return 2 * d + 64; }   // == 64 mod 128
+  __host__ __device__ static constexpr int h_stride(int d) { return 8 * d + 64; }   // == 64 mod 128
+  __host__ __device__ static constexpr int a_off(int d) { return (kX + kDsRows * x_stride(d) + 127) & ~127; }
+  __host__ __device__ static constexpr int h_off(int d) { return a_off(d) + kDsRows * a_stride(d); }
+  __host__ __device__ static constexpr int ring(int d) { return (h_off(d) + kDsRows * h_stride(d) + 1023) & ~1023; }
   __host__ __device__ static constexpr int total(int d, int n_stages) { return ring(d) + n_stages * kDsStageBytes; }
 };
 
@@ -119,26 +121,59 @@ __device__ __forceinline__ uint64_t l2_evict_last_policy() {
   asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
   return p;
 }
+// address of the same shared-memory location in CTA `cta` of the cluster
+__device__ __forceinline__ uint32_t ds_mapa(uint32_t addr, int cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(cta));
+  return r;
+}
+__device__ __forceinline__ void ds_st_remote(uint32_t raddr, uint32_t v) {
+  asm volatile("st.shared::cluster.b32 [%0], %1;" ::"r"(raddr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void ds_st_remote(uint32_t raddr, float2 v) {
+  asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(raddr), "f"(v.x), "f"(v.y) : "memory");
+}
+__device__ __forceinline__ void ds_st_remote(uint32_t raddr, unsigned long long v) {
+  asm volatile("st.shared::cluster.b64 [%0], %1;" ::"r"(raddr), "l"(v) : "memory");
+}
+// the same value into the same location of every CTA of the cluster (own copy included)
+template <class T>
+__device__ __forceinline__ void ds_push_all(uint32_t local_addr, T v, int G) {
+  for (int c = 0; c < G; ++c) ds_st_remote(ds_mapa(local_addr, c), v);
+}
 
 __device__ __forceinline__ uint64_t* ds_full(uint8_t* smem) { return reinterpret_cast<uint64_t*>(smem + DsSmem::kBars); }
 __device__ __forceinline__ uint64_t* ds_empty(uint8_t* smem) { return ds_full(smem) + kDsMaxStages; }
 __device__ __forceinline__ uint64_t* ds_cbar(uint8_t* smem) { return ds_full(smem) + 2 * kDsMaxStages; }
 __device__ __forceinline__ DsStream* ds_stream(uint8_t* smem) { return reinterpret_cast<DsStream*>(smem + DsSmem::kStream); }
-__device__ __forceinline__ int4* ds_segs(uint8_t* smem) { return reinterpret_cast<int4*>(smem + DsSmem::kSegs); }
+__device__ __forceinline__ int* ds_tok(uint8_t* smem) { return reinterpret_cast<int*>(smem + DsSmem::kTok); }
+__device__ __forceinline__ int* ds_done(uint8_t* smem) { return ds_tok(smem) + kDsRows; }
+// owner CTA of (clip, head) pair `pr` under the balanced split, and the pair's index inside the owner's range
+__device__ __forceinline__ void ds_pair_owner(const DsStream* st, int pr, int& cta, int& idx) {
+  const int base = st->pair_base, rem = st->pair_rem, cut = rem * (base + 1);
+  if (pr < cut) {
+    cta = pr / (base + 1);
+    idx = pr - cta * (base + 1);
+  } else {
+    const int q = (pr - cut) / base;   // base >= 1 whenever pr >= cut exists
+    cta = rem + q;
+    idx = (pr - cut) - q * base;
+  }
+}
 
-// Cluster-wide barrier of the CONSUMER warps: CTA-level named barrier, then one remote arrive per peer (lane i of
-// warp 0 -> CTA i's mbarrier, release at cluster scope — cumulative over the CTA's writes ordered by the named
-// barrier), then every consumer thread waits for its own CTA's mbarrier phase (acquire at cluster scope). Data other
-// CTAs wrote to global memory is read afterwards with L1-bypassing loads (__ldcg).
+// Cluster-wide barrier of the CONSUMER warps. Every consumer thread first fences its own pushes / global stores at
+// cluster scope; then a CTA-level named barrier, one remote arrive per peer (lane i of warp 0 -> CTA i's mbarrier,
+// release at cluster scope), and every consumer thread waits for its own CTA's mbarrier phase (acquire at cluster
+// scope). Data peers left in global memory (KV cache, qs) is read afterwards with L1-bypassing loads (__ldcg).
 __device__ __forceinline__ void ds_cluster_sync(uint8_t* smem, const DsParams& p, unsigned& cphase, int kind,
                                                 unsigned long long& tlast) {
   const bool tr = p.trace != nullptr && threadIdx.x == 0;
   const unsigned long long t_arr = tr ? dec_globaltimer() : 0ull;
+  asm volatile("fence.acq_rel.cluster;" ::: "memory");
   ds_cons_bar();
   const uint32_t local = smem_u32(ds_cbar(smem));
   if (threadIdx.x < (unsigned)p.G) {
-    uint32_t remote;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(threadIdx.x));
+    const uint32_t remote = ds_mapa(local, (int)threadIdx.x);
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
   }
   asm volatile(
@@ -209,108 +244,42 @@ __global__ void ds_fold_bias_kernel(const __nv_bfloat16* __restrict__ W, const f
   if (lane == 0) out[warp] = s + (b ? b[warp] : 0.0f);
 }
 
+
 // ---------------------------------------------------------------------------------------------------
-// Activation tile: rows_pad = 16 rows x K bf16 in shared memory, row stride `as` bytes (== 64 mod 128, so the 16-byte
-// fragment loads of a quarter warp — 2 rows x 4 k pieces — cover all 32 banks once).
+// LayerNorm (gain/bias folded into the packed weights) of the residual copy sX -> MMA operand tile sA: one warp per
+// row, shared memory to shared memory, no global access.
 // ---------------------------------------------------------------------------------------------------
-// LayerNorm without gain/bias (both folded into the packed weights): one warp per row, the row in registers
-__device__ __forceinline__ void ds_stage_norm(uint8_t* sA, int as, const float* x, int n_clips, int d) {
+__device__ __forceinline__ void ds_stage_norm(uint8_t* smem, int n_clips, int d) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int per = d >> 7;  // float4 per lane (d multiple of 128) — d = 64 handled by the tail path below
-  for (int r = warp; r < kDsRows; r += kDsConsWarps) {
-    uint8_t* dst = sA + (size_t)r * as;
-    if (r < n_clips && per > 0) {
-      float4 v[kDecMaxD / 128];
-      float s = 0.0f;
+  const uint8_t* sX = smem + DsSmem::kX;
+  uint8_t* sA = smem + DsSmem::a_off(d);
+  const int xs = DsSmem::x_stride(d), as = DsSmem::a_stride(d);
+  const int per = d >> 6;  // bf16 pairs per lane
+  for (int r = warp; r < n_clips; r += kDsConsWarps) {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(sX + (size_t)r * xs);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(sA + (size_t)r * as);
+    float2 v[kDecMaxD / 64];
+    float s = 0.0f;
 #pragma unroll
-      for (int i = 0; i < kDecMaxD / 128; ++i)
-        if (i < per) {
-          v[i] = __ldcg(reinterpret_cast<const float4*>(x + (size_t)r * d + i * 128 + 4 * lane));
-          s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
-        }
-      const float mean = warp_sum(s) / (float)d;
-      float q = 0.0f;
+    for (int i = 0; i < kDecMaxD / 64; ++i)
+      if (i < per) {
+        const uint32_t w = src[i * 32 + lane];
+        v[i] = make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+        s += v[i].x + v[i].y;
+      }
+    const float mean = warp_sum(s) / (float)d;
+    float q = 0.0f;
 #pragma unroll
-      for (int i = 0; i < kDecMaxD / 128; ++i)
-        if (i < per) {
-          v[i].x -= mean; v[i].y -= mean; v[i].z -= mean; v[i].w -= mean;
-          q += (v[i].x * v[i].x + v[i].y * v[i].y) + (v[i].z * v[i].z + v[i].w * v[i].w);
-        }
-      const float rstd = rsqrtf(warp_sum(q) / (float)d + 1e-5f);
+    for (int i = 0; i < kDecMaxD / 64; ++i)
+      if (i < per) {
+        v[i].x -= mean;
+        v[i].y -= mean;
+        q += v[i].x * v[i].x + v[i].y * v[i].y;
+      }
+    const float rstd = rsqrtf(warp_sum(q) / (float)d + 1e-5f);
 #pragma unroll
-      for (int i = 0; i < kDecMaxD / 128; ++i)
-        if (i < per)
-          *reinterpret_cast<uint2*>(dst + (i * 128 + 4 * lane) * 2) =
-              make_uint2(dec_pack2(v[i].x * rstd, v[i].y * rstd), dec_pack2(v[i].z * rstd, v[i].w * rstd));
-    } else if (r < n_clips) {
-      // d not a multiple of 128 (test-sized models): two elements per lane and pass
-      float s = 0.0f;
-      for (int c = 2 * lane; c < d; c += 64) {
-        const float2 t = __ldcg(reinterpret_cast<const float2*>(x + (size_t)r * d + c));
-        s += t.x + t.y;
-      }
-      const float mean = warp_sum(s) / (float)d;
-      float q = 0.0f;
-      for (int c = 2 * lane; c < d; c += 64) {
-        const float2 t = __ldcg(reinterpret_cast<const float2*>(x + (size_t)r * d + c));
-        q += (t.x - mean) * (t.x - mean) + (t.y - mean) * (t.y - mean);
-      }
-      const float rstd = rsqrtf(warp_sum(q) / (float)d + 1e-5f);
-      for (int c = 2 * lane; c < d; c += 64) {
-        const float2 t = __ldcg(reinterpret_cast<const float2*>(x + (size_t)r * d + c));
-        *reinterpret_cast<uint32_t*>(dst + c * 2) = dec_pack2((t.x - mean) * rstd, (t.y - mean) * rstd);
-      }
-    } else {
-      for (int c = lane; c < (d >> 1); c += 32) reinterpret_cast<uint32_t*>(dst)[c] = 0u;
-    }
-  }
-}
-__device__ __forceinline__ void ds_stage_f32(uint8_t* sA, int as, const float* src, int n_clips, int d) {
-  const int per_row = d >> 2;
-  for (int i = threadIdx.x; i < kDsRows * per_row; i += kDsConsThreads) {
-    const int r = i / per_row, c = (i - r * per_row) * 4;
-    uint2 o = make_uint2(0u, 0u);
-    if (r < n_clips) {
-      const float4 v = __ldcg(reinterpret_cast<const float4*>(src + (size_t)r * d + c));
-      o = make_uint2(dec_pack2(v.x, v.y), dec_pack2(v.z, v.w));
-    }
-    *reinterpret_cast<uint2*>(sA + (size_t)r * as + c * 2) = o;
-  }
-}
-__device__ __forceinline__ void ds_stage_bf16(uint8_t* sA, int as, const __nv_bfloat16* src, int n_clips, int K) {
-  const int per_row = K >> 3;
-  for (int i = threadIdx.x; i < kDsRows * per_row; i += kDsConsThreads) {
-    const int r = i / per_row, c = (i - r * per_row) * 8;
-    uint4 o = make_uint4(0u, 0u, 0u, 0u);
-    if (r < n_clips) o = __ldcg(reinterpret_cast<const uint4*>(src + (size_t)r * K + c));
-    *reinterpret_cast<uint4*>(sA + (size_t)r * as + c * 2) = o;
-  }
-}
-// cross-attention output = softmax-merge of the per-CTA partials (acc[64], max, sum) of every CTA covering the pair
-__device__ __forceinline__ void ds_stage_xmerge(uint8_t* sA, int as, const DsParams& p, int per, int cpp, int n_clips,
-                                                int d) {
-  const int half = d >> 1;
-  for (int i = threadIdx.x; i < kDsRows * half; i += kDsConsThreads) {
-    const int r = i / half, c = (i - r * half) * 2;
-    uint32_t o = 0u;
-    if (r < n_clips) {
-      const int pr = r * p.H + (c >> 6), e = c & 63;
-      const int first = (pr * cpp) / per, last = ((pr + 1) * cpp - 1) / per;
-      const float* p0 = p.xpart + (size_t)pr * p.xslots * 66;
-      float M = -1.0e30f;
-      for (int k = 0; k <= last - first; ++k) M = fmaxf(M, __ldcg(p0 + k * 66 + 64));
-      float Lw = 0.0f, o0 = 0.0f, o1 = 0.0f;
-      for (int k = 0; k <= last - first; ++k) {
-        const float s1 = dec_ex2(__ldcg(p0 + k * 66 + 64) - M);
-        const float2 a2 = __ldcg(reinterpret_cast<const float2*>(p0 + k * 66 + e));
-        Lw = fmaf(__ldcg(p0 + k * 66 + 65), s1, Lw);
-        o0 = fmaf(a2.x, s1, o0);
-        o1 = fmaf(a2.y, s1, o1);
-      }
-      const float inv = 1.0f / Lw;
-      o = dec_pack2(o0 * inv, o1 * inv);
-    }
-    *reinterpret_cast<uint32_t*>(sA + (size_t)r * as + c * 2) = o;
+    for (int i = 0; i < kDecMaxD / 64; ++i)
+      if (i < per) dst[i * 32 + lane] = dec_pack2(v[i].x * rstd, v[i].y * rstd);
   }
 }
 
@@ -356,38 +325,33 @@ __device__ __forceinline__ void ds_mma_round(uint8_t* smem, const DsParams& p, D
   for (int j = 0; j < 4; ++j) acc[j] = a0[j] + a1[j];
 }
 
-// ---- projections: stage the activation tile, then rounds of (MMA over the ring, epilogue on the fragment) ----
-__device__ __noinline__ void ds_gemm(uint8_t* smem, const DsParams& p, DsRing& rg, int kind, int l, int pos) {
+// ---- projections: (LayerNorm into the operand tile,) rounds of MMA over the ring, epilogue on the fragment.
+//      xr = this lane's elements of the residual stream (rows g / g+8 of its columns), kept in registers for the whole
+//      launch: the residual projections (OUT, XOUT, FC2) always land on the same columns of the same warps. ----
+__device__ __forceinline__ void ds_gemm(uint8_t* smem, const DsParams& p, DsRing& rg, int kind, int l, int pos,
+                                        float2 (&xr)[2][2]) {
   const DsLayerDev& L = p.layers[l];
   const DsStream* st = ds_stream(smem);
-  const int d = p.d, B = p.n_clips, as = DsSmem::a_stride(d);
-  uint8_t* sA = smem + DsSmem::kA;
-  switch (kind) {
-    case DS_OUT: ds_stage_f32(sA, as, p.att, B, d); break;
-    case DS_XOUT: ds_stage_xmerge(sA, as, p, st->per, st->cpp, B, d); break;
-    case DS_FC2: ds_stage_bf16(sA, as, p.hmid, B, 4 * d); break;
-    default: ds_stage_norm(sA, as, p.x, B, d); break;  // QKV, XQ, FC1: LayerNorm (gain/bias folded into W, b)
+  const int d = p.d, B = p.n_clips, G = p.G;
+  const bool from_h = kind == DS_FC2;
+  if (kind == DS_QKV || kind == DS_XQ || kind == DS_FC1) {
+    ds_stage_norm(smem, B, d);
+    ds_cons_bar();
   }
-  ds_cons_bar();
+  const int as = from_h ? DsSmem::h_stride(d) : DsSmem::a_stride(d);
+  const uint8_t* sA = smem + (from_h ? DsSmem::h_off(d) : DsSmem::a_off(d));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int ng = st->ng[kind], kph = st->kph[kind];
   const int g0 = (int)(st->slice_unit0[kind] / (kph * p.upw));  // first group of this CTA's slice
   const float* bias = L.b[kind];
   const uint8_t* ring = smem + DsSmem::ring(d);
   const uint8_t* a_lane = sA + (size_t)g * as + t * 16;
-  const bool resid = kind == DS_OUT || kind == DS_XOUT || kind == DS_FC2;
   const bool r0 = g < B, r1 = g + 8 < B;
   for (int rho = 0; rho * 8 < ng; ++rho) {
     const bool active = rho * 8 + warp < ng;
     const int n = (g0 + rho * 8 + warp) * 8 + 2 * t;  // this lane's first column
-    float2 bz = make_float2(0.0f, 0.0f), x0 = bz, x1 = bz;
-    if (active) {
-      bz = __ldg(reinterpret_cast<const float2*>(bias + n));
-      if (resid) {
-        if (r0) x0 = __ldcg(reinterpret_cast<const float2*>(p.x + (size_t)g * d + n));
-        if (r1) x1 = __ldcg(reinterpret_cast<const float2*>(p.x + (size_t)(g + 8) * d + n));
-      }
-    }
+    float2 bz = make_float2(0.0f, 0.0f);
+    if (active) bz = __ldg(reinterpret_cast<const float2*>(bias + n));
     float acc[4];
     ds_mma_round(smem, p, rg, ring, a_lane, as, kph, active, acc);
     if (!active) continue;
@@ -405,31 +369,83 @@ __device__ __noinline__ void ds_gemm(uint8_t* smem, const DsParams& p, DsRing& r
           if (r1) *reinterpret_cast<uint32_t*>(cache + ((size_t)(p.clip0 + g + 8) * p.H + hh) * 32 * 64 + col) = dec_pack2(v10, v11);
         }
         break;
-      case DS_XQ:
-        if (r0) *reinterpret_cast<float2*>(p.qx + (size_t)g * d + n) = make_float2(v00, v01);
-        if (r1) *reinterpret_cast<float2*>(p.qx + (size_t)(g + 8) * d + n) = make_float2(v10, v11);
+      case DS_XQ: {
+        // the query goes (pre-scaled, f32) straight to the CTA that owns the (clip, head) pair's K/V range
+        const float qscale = 0.125f * 1.4426950408889634f;
+        const int hh = n >> 6, e = n & 63;
+        const uint32_t xq = smem_u32(smem + DsSmem::kXq);
+        int cta, idx;
+        if (r0) {
+          ds_pair_owner(st, g * p.H + hh, cta, idx);
+          ds_st_remote(ds_mapa(xq + (idx * 64 + e) * 4, cta), make_float2(v00 * qscale, v01 * qscale));
+        }
+        if (r1) {
+          ds_pair_owner(st, (g + 8) * p.H + hh, cta, idx);
+          ds_st_remote(ds_mapa(xq + (idx * 64 + e) * 4, cta), make_float2(v10 * qscale, v11 * qscale));
+        }
         break;
-      case DS_FC1:
-        if (r0) *reinterpret_cast<uint32_t*>(p.hmid + (size_t)g * 4 * d + n) = dec_pack2(gelu_erf(v00), gelu_erf(v01));
-        if (r1) *reinterpret_cast<uint32_t*>(p.hmid + (size_t)(g + 8) * 4 * d + n) = dec_pack2(gelu_erf(v10), gelu_erf(v11));
+      }
+      case DS_FC1: {
+        const uint32_t sh = smem_u32(smem + DsSmem::h_off(d)) + n * 2;
+        const int hs = DsSmem::h_stride(d);
+        if (r0) ds_push_all(sh + g * hs, dec_pack2(gelu_erf(v00), gelu_erf(v01)), G);
+        if (r1) ds_push_all(sh + (g + 8) * hs, dec_pack2(gelu_erf(v10), gelu_erf(v11)), G);
         break;
-      default:  // residual update
-        if (r0) *reinterpret_cast<float2*>(p.x + (size_t)g * d + n) = make_float2(x0.x + v00, x0.y + v01);
-        if (r1) *reinterpret_cast<float2*>(p.x + (size_t)(g + 8) * d + n) = make_float2(x1.x + v10, x1.y + v11);
+      }
+      default: {  // residual update: registers, and a bf16 copy into every CTA's sX for the next LayerNorm
+        const uint32_t sx = smem_u32(smem + DsSmem::kX) + n * 2;
+        const int xs = DsSmem::x_stride(d);
+        auto upd = [&](float2(&x)[2]) {   // constant register indices on both paths
+          x[0].x += v00; x[0].y += v01; x[1].x += v10; x[1].y += v11;
+          if (r0) ds_push_all(sx + g * xs, dec_pack2(x[0].x, x[0].y), G);
+          if (r1) ds_push_all(sx + (g + 8) * xs, dec_pack2(x[1].x, x[1].y), G);
+        };
+        if (rho & 1) upd(xr[1]); else upd(xr[0]);
         break;
+      }
     }
   }
 }
 
-// ---- final LayerNorm -> tied logits with a fused (max, last index) per row (whisper.cpp:346-361's tie rule) ----
+// x[b] = tok_emb[token(b, pos)] + pos_emb[pos], computed by the owners of the residual columns (the DS_OUT slice)
+__device__ __forceinline__ void ds_embed(uint8_t* smem, const DsParams& p, int pos, float2 (&xr)[2][2]) {
+  const DsStream* st = ds_stream(smem);
+  const int d = p.d, B = p.n_clips, G = p.G;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int ng = st->ng[DS_OUT];
+  const int g0 = (int)(st->slice_unit0[DS_OUT] / (st->kph[DS_OUT] * p.upw));
+  const int* s_tok = ds_tok(smem);
+  const uint32_t sxb = smem_u32(smem + DsSmem::kX);
+  const int xs = DsSmem::x_stride(d);
+  for (int rho = 0; rho * 8 < ng; ++rho) {
+    if (rho * 8 + warp >= ng) continue;
+    const int n = (g0 + rho * 8 + warp) * 8 + 2 * t;
+    const __nv_bfloat162 e = *reinterpret_cast<const __nv_bfloat162*>(p.pos_emb + (size_t)pos * d + n);
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int r = g + 8 * hh;
+      if (r < B) {
+        int tok = (pos < p.prompt_len) ? __ldg(p.tokens + (size_t)(p.clip0 + r) * kDecTokStride + pos) : s_tok[r];
+        if (tok < 0) tok = 0;
+        const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(p.tok_emb + (size_t)tok * d + n);
+        const float2 x = make_float2(__bfloat162float(a.x) + __bfloat162float(e.x), __bfloat162float(a.y) + __bfloat162float(e.y));
+        if (rho & 1) xr[1][hh] = x; else xr[0][hh] = x;
+        ds_push_all(sxb + r * xs + n * 2, dec_pack2(x.x, x.y), G);
+      }
+    }
+  }
+}
+
+// ---- final LayerNorm -> tied logits with a fused (max, last index) per row (whisper.cpp:346-361's tie rule); this
+//      CTA's winners go to every peer's s_amax[rank][row] ----
 __device__ __noinline__ void ds_logits(uint8_t* smem, const DsParams& p, DsRing& rg, int pos) {
   const DsStream* st = ds_stream(smem);
   const int d = p.d, B = p.n_clips, V = p.V, as = DsSmem::a_stride(d);
-  uint8_t* sA = smem + DsSmem::kA;
-  unsigned long long* s_best = reinterpret_cast<unsigned long long*>(smem + DsSmem::kBest);
+  const uint8_t* sA = smem + DsSmem::a_off(d);
+  unsigned long long* s_best = reinterpret_cast<unsigned long long*>(smem + DsSmem::kMisc);  // [16], merge scratch is idle
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   if (tid < kDsRows) s_best[tid] = 0ull;
-  ds_stage_norm(sA, as, p.x, B, d);
+  ds_stage_norm(smem, B, d);
   ds_cons_bar();
   const int ng = st->ng[DS_LOGITS], kph = st->kph[DS_LOGITS];
   const int g0 = (int)(st->slice_unit0[DS_LOGITS] / (kph * p.upw));
@@ -478,15 +494,46 @@ __device__ __noinline__ void ds_logits(uint8_t* smem, const DsParams& p, DsRing&
     if (best1 != 0ull) atomicMax(s_best + g + 8, best1);
   }
   ds_cons_bar();
-  if (tid < B) p.amax_part[(size_t)tid * kDecMaxCluster + p.rank] = s_best[tid];
+  if (tid < B) ds_push_all(smem_u32(smem + DsSmem::kAmax) + (p.rank * kDsRows + tid) * 8, s_best[tid], p.G);
 }
 
-// ---- self-attention over cache rows 0..pos: one warp per (clip, head), lane = key ----
+// ---- every CTA reduces the cluster's partial winners itself (identical results everywhere): token of the step, EOT
+//      bookkeeping; CTA 0 publishes tokens / lens / done. Returns the number of clips that have produced EOT. ----
+__device__ __forceinline__ int ds_finalize(uint8_t* smem, const DsParams& p, int pos) {
+  const int tid = threadIdx.x;
+  const unsigned long long* s_amax = reinterpret_cast<const unsigned long long*>(smem + DsSmem::kAmax);
+  int* s_tok = ds_tok(smem);
+  int* s_done = ds_done(smem);
+  if (tid < p.n_clips) {
+    unsigned long long v = 0ull;
+    for (int c = 0; c < p.G; ++c) v = u64_max(v, s_amax[c * kDsRows + tid]);
+    const int tok = (int)(v & 0xffffffffull);
+    if (!s_done[tid]) {
+      s_tok[tid] = tok;
+      if (tok == p.eot) s_done[tid] = 1;
+      if (p.rank == 0) {
+        const int cb = p.clip0 + tid;
+        p.tokens[(size_t)cb * kDecTokStride + pos + 1] = tok;
+        p.lens[cb] = pos + 2;
+        if (tok == p.eot) p.done[cb] = 1;
+      }
+    }
+  }
+  ds_cons_bar();
+  int fin = 0;
+  for (int r = 0; r < p.n_clips; ++r) fin += s_done[r];
+  return fin;
+}
+
+// ---- self-attention over cache rows 0..pos: one warp per (clip, head), lane = key; the output row segment goes, as
+//      bf16, into every CTA's operand tile (it is the A operand of the out-projection) ----
 __device__ __noinline__ void ds_self_attn(uint8_t* smem, const DsParams& p, const DsLayerDev& L, int pos) {
   float* s_misc = reinterpret_cast<float*>(smem + DsSmem::kMisc);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int d = p.d, H = p.H, B = p.n_clips;
   float* sq = s_misc + 16 + warp * 64;
+  const uint32_t sa = smem_u32(smem + DsSmem::a_off(d));
+  const int as = DsSmem::a_stride(d);
   for (int pr = p.rank * kDsConsWarps + warp; pr < B * H; pr += p.G * kDsConsWarps) {
     const int b = pr / H, h = pr - b * H;
     const size_t base = ((size_t)(p.clip0 + b) * H + h) * 32 * 64;
@@ -524,39 +571,32 @@ __device__ __noinline__ void ds_self_attn(uint8_t* smem, const DsParams& p, cons
       o1 = fmaf(pj, __uint_as_float(vv[j] & 0xffff0000u), o1);
     }
     const float inv = 1.0f / lsum;
-    *reinterpret_cast<float2*>(p.att + (size_t)b * d + h * 64 + 2 * lane) = make_float2(o0 * inv, o1 * inv);
+    ds_push_all(sa + b * as + (h * 64 + 2 * lane) * 2, dec_pack2(o0 * inv, o1 * inv), p.G);
     __syncwarp();
   }
 }
 
-// ---- cross-attention: the group's (clip, head, chunk) space is cut into one contiguous range per CTA; the chunks of
-//      that range arrive through the ring in order. 8 lanes share a key (8 dims each), 4 keys per warp and load. ----
+// ---- cross-attention: this CTA owns whole (clip, head) pairs; their K/V chunks arrive through the ring in order,
+//      their queries were pushed into s_q by the query projection's epilogue. 8 lanes share a key (8 dims each), 4 keys
+//      per warp and load. The finished 64-wide output goes, as bf16, into every CTA's operand tile. ----
 __device__ __noinline__ void ds_cross_attn(uint8_t* smem, const DsParams& p, DsRing& rg) {
   float* s_misc = reinterpret_cast<float*>(smem + DsSmem::kMisc);
-  float* s_q = reinterpret_cast<float*>(smem + DsSmem::kXq);
+  const float* s_q = reinterpret_cast<const float*>(smem + DsSmem::kXq);
   const uint8_t* ring = smem + DsSmem::ring(p.d);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int grp = lane >> 3, sub = lane & 7;
   const int d = p.d, H = p.H, S = p.S;
   const DsStream* st = ds_stream(smem);
-  const int4* segs = ds_segs(smem);
-  const int nseg = st->nseg, per = st->per, cpp = st->cpp;
+  const int cpp = st->cpp;
   uint64_t* full = ds_full(smem);
   uint64_t* empty = ds_empty(smem);
   float* sm_m = s_misc;             // [8]
   float* sm_l = s_misc + 8;         // [8]
   float* sm_acc = s_misc + 16;      // [8][64]
-  {
-    const float qscale = 0.125f * 1.4426950408889634f;
-    for (int i = tid; i < nseg * 64; i += kDsConsThreads) {
-      const int pr = segs[i >> 6].x, b = pr / H, h = pr - b * H;
-      s_q[i] = __ldcg(p.qx + (size_t)b * d + h * 64 + (i & 63)) * qscale;
-    }
-  }
-  ds_cons_bar();
-  for (int si = 0; si < nseg; ++si) {
-    const int4 sg = segs[si];  // {pair, first chunk, end chunk, ...}
-    const int pr = sg.x;
+  const uint32_t sa = smem_u32(smem + DsSmem::a_off(d));
+  const int as = DsSmem::a_stride(d);
+  for (int si = 0; si < st->npairs; ++si) {
+    const int pr = st->pair0 + si;
     float qv[8];
     {
       const float4 q0 = *reinterpret_cast<const float4*>(s_q + si * 64 + sub * 8);
@@ -567,7 +607,7 @@ __device__ __noinline__ void ds_cross_attn(uint8_t* smem, const DsParams& p, DsR
     float m = -1.0e30f, lsum = 0.0f, acc[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[i] = 0.0f;
-    for (int c = sg.y; c < sg.z; ++c) {
+    for (int c = 0; c < cpp; ++c) {
       const int n_keys = (S - c * kXaChunk < kXaChunk) ? S - c * kXaChunk : kXaChunk;
       mbar_wait(full + rg.slot, rg.par);
       const uint8_t* stg = ring + (size_t)rg.slot * kDsStageBytes;
@@ -635,7 +675,7 @@ __device__ __noinline__ void ds_cross_attn(uint8_t* smem, const DsParams& p, DsR
       }
       m = mn;
     }
-    ds_cons_bar();  // s_misc free (previous segment's merge done)
+    ds_cons_bar();  // s_misc free (previous pair's merge done)
     if (grp == 0) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) sm_acc[warp * 64 + sub * 8 + i] = acc[i];
@@ -645,68 +685,22 @@ __device__ __noinline__ void ds_cross_attn(uint8_t* smem, const DsParams& p, DsR
       }
     }
     ds_cons_bar();
-    // this CTA's partial (acc[64], max, sum) of pair `pr` goes to its slot; the out-projection's staging merges the
-    // slots of all CTAs that cover the pair after the cluster barrier
-    if (tid < 64) {
-      const int first_cta = (pr * cpp) / per;
-      float* pp = p.xpart + ((size_t)pr * p.xslots + (p.rank - first_cta)) * 66;
+    if (tid < 32) {
       float M = sm_m[0];
 #pragma unroll
       for (int w = 1; w < kDsConsWarps; ++w) M = fmaxf(M, sm_m[w]);
-      float Lw = 0.0f, O = 0.0f;
+      float Lw = 0.0f, o0 = 0.0f, o1 = 0.0f;
 #pragma unroll
       for (int w = 0; w < kDsConsWarps; ++w) {
         const float s1 = dec_ex2(sm_m[w] - M);
+        const float2 a2 = *reinterpret_cast<const float2*>(sm_acc + w * 64 + 2 * tid);
         Lw = fmaf(sm_l[w], s1, Lw);
-        O = fmaf(sm_acc[w * 64 + tid], s1, O);
+        o0 = fmaf(a2.x, s1, o0);
+        o1 = fmaf(a2.y, s1, o1);
       }
-      pp[tid] = O;
-      if (tid == 0) {
-        pp[64] = M;
-        pp[65] = Lw;
-      }
-    }
-  }
-}
-
-// ---- finalize (CTA b): append the winner, EOT bookkeeping ----
-__device__ __noinline__ void ds_finalize(uint8_t* smem, const DsParams& p, int pos) {
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int G = p.G;
-  // one warp per clip: lanes read the G per-CTA partial winners
-  for (int b = p.rank * kDsConsWarps + warp; b < p.n_clips; b += G * kDsConsWarps) {
-    unsigned long long v = 0ull;
-    if (lane < G) v = __ldcg(p.amax_part + (size_t)b * kDecMaxCluster + lane);
-    v = warp_max_u64(v);
-    if (lane == 0) {
-      const int tok = (int)(v & 0xffffffffull);
-      const int cb = p.clip0 + b;
-      if (!p.done[cb]) {
-        p.tokens[(size_t)cb * kDecTokStride + pos + 1] = tok;
-        p.lens[cb] = pos + 2;
-        if (tok == p.eot) {
-          p.done[cb] = 1;
-          atomicAdd(p.finished, 1);
-        }
-      }
-    }
-    __syncwarp();  // ds_embed (same warp, same clip) reads the token lane 0 just appended
-  }
-}
-
-// x[b] = tok_emb[token(b, pos)] + pos_emb[pos]   (a finished clip keeps stepping on its last token, unused)
-__device__ __noinline__ void ds_embed(const DsParams& p, int pos) {
-  const int d = p.d, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int b = p.rank * kDsConsWarps + warp; b < p.n_clips; b += p.G * kDsConsWarps) {
-    int tok = __ldcg(p.tokens + (size_t)(p.clip0 + b) * kDecTokStride + pos);
-    if (tok < 0) tok = 0;
-    const __nv_bfloat16* te = p.tok_emb + (size_t)tok * d;
-    const __nv_bfloat16* pe = p.pos_emb + (size_t)pos * d;
-    for (int c = 2 * lane; c < d; c += 64) {
-      const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(te + c);
-      const __nv_bfloat162 e = *reinterpret_cast<const __nv_bfloat162*>(pe + c);
-      *reinterpret_cast<float2*>(p.x + (size_t)b * d + c) =
-          make_float2(__bfloat162float(a.x) + __bfloat162float(e.x), __bfloat162float(a.y) + __bfloat162float(e.y));
+      const float inv = 1.0f / Lw;
+      const int b = pr / H, h = pr - b * H;
+      ds_push_all(sa + b * as + (h * 64 + 2 * tid) * 2, dec_pack2(o0 * inv, o1 * inv), p.G);
     }
   }
 }
@@ -717,7 +711,6 @@ __device__ __noinline__ void ds_embed(const DsParams& p, int pos) {
 // free ring stages. Returns the number of stages issued.
 // ---------------------------------------------------------------------------------------------------
 struct DsProd {
-  uint8_t* smem;
   uint8_t* ring;
   uint64_t *full, *empty;
   DsStream* st;
@@ -751,15 +744,13 @@ struct DsProd {
 
 __device__ __noinline__ unsigned ds_producer(uint8_t* smem, const DsParams& p) {
   DsProd pr;
-  pr.smem = smem;
   pr.ring = smem + DsSmem::ring(p.d);
   pr.full = ds_full(smem);
   pr.empty = ds_empty(smem);
   pr.st = ds_stream(smem);
   pr.n = 0; pr.slot = 0; pr.par = 0; pr.n_stages = p.n_stages;
   const uint64_t pol_kv = l2_evict_first_policy(), pol_w = l2_evict_last_policy();
-  const int4* segs = ds_segs(smem);
-  const int nseg = pr.st->nseg, cpp = pr.st->cpp, upw = p.upw;
+  const int pair0 = pr.st->pair0, npairs = pr.st->npairs, cpp = pr.st->cpp, upw = p.upw;
   const size_t chunk_elems = (size_t)2 * kXaChunk * 64;
   for (int pos = 0; pos <= p.max_total - 2; ++pos) {
     for (int l = 0; l < p.n_layers; ++l) {
@@ -767,10 +758,9 @@ __device__ __noinline__ unsigned ds_producer(uint8_t* smem, const DsParams& p) {
       if (!pr.weights(L.w[DS_QKV], DS_QKV, upw, pol_w)) return pr.n;
       if (!pr.weights(L.w[DS_OUT], DS_OUT, upw, pol_w)) return pr.n;
       if (!pr.weights(L.w[DS_XQ], DS_XQ, upw, pol_w)) return pr.n;
-      for (int si = 0; si < nseg; ++si) {
-        const int4 sg = segs[si];
-        const __nv_bfloat16* src = L.kvx + (((size_t)p.clip0 * p.H + sg.x) * cpp + sg.y) * chunk_elems;
-        for (int c = sg.y; c < sg.z; ++c, src += chunk_elems)
+      {
+        const __nv_bfloat16* src = L.kvx + ((size_t)p.clip0 * p.H + pair0) * cpp * chunk_elems;
+        for (int c = 0; c < npairs * cpp; ++c, src += chunk_elems)
           if (!pr.issue(src, (uint32_t)kDsStageBytes, pol_kv)) return pr.n;
       }
       if (!pr.weights(L.w[DS_XOUT], DS_XOUT, upw, pol_w)) return pr.n;
@@ -788,7 +778,7 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
   extern __shared__ __align__(1024) uint8_t ds_smem[];
   const int tid = threadIdx.x, warp = tid >> 5;
   DsParams& p = *reinterpret_cast<DsParams*>(ds_smem + DsSmem::kParams);
-  static_assert(sizeof(DsParams) <= 512, "DsParams outgrew its shared-memory slot");
+  static_assert(sizeof(DsParams) <= 256, "DsParams outgrew its shared-memory slot");
   static_assert(sizeof(DsStream) <= 256, "DsStream outgrew its shared-memory slot");
   static_assert(sizeof(DsLayerDev) == 128, "DsLayerDev slot size");
   const int G = (int)dec_cluster_nctarank();
@@ -804,18 +794,10 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
     p.rank = rank;
     p.clip0 = p_in.clip0 + first;
     p.n_clips = nb;
-    const size_t row0 = (size_t)group * kDsRows;
-    p.x += row0 * p.d;
-    p.qs += row0 * p.d;
-    p.att += row0 * p.d;
-    p.qx += row0 * p.d;
-    p.hmid += row0 * 4 * p.d;
-    p.xpart += row0 * p.H * (size_t)p.xslots * 66;
-    p.amax_part += row0 * kDecMaxCluster;
-    p.finished += group;
+    p.qs += (size_t)group * kDsRows * p.d;
     if (group != 0 || rank != 0) p.trace = nullptr;
     p.layers = reinterpret_cast<const DsLayerDev*>(ds_smem + DsSmem::kLayers);
-    // ---- this CTA's stream: weight slices per kind, cross-attention range ----
+    // ---- this CTA's stream: weight slices per kind, cross-attention pairs ----
     DsStream* st = ds_stream(ds_smem);
     const int d = p.d;
     for (int k = 0; k < DS_NKIND; ++k) {
@@ -828,26 +810,12 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
       st->kph[k] = kbK / p.upw;
       st->slice_unit0[k] = (long long)rank * gpc * kbK;
     }
-    int4* segs = ds_segs(ds_smem);
-    const int cpp = (p.S + kXaChunk - 1) / kXaChunk;
-    const int T = nb * p.H * cpp;
-    const int per = (T + G - 1) / G;
-    int cur = rank * per;
-    const int hi = (cur + per < T) ? cur + per : T;
-    int nseg = 0, nchunks = 0;
-    while (cur < hi && nseg < kDsMaxSeg) {
-      const int pr = cur / cpp;
-      const int c0 = cur - pr * cpp;
-      const int c1 = (hi - cur < cpp - c0) ? c0 + (hi - cur) : cpp;
-      segs[nseg] = make_int4(pr, c0, c1, nchunks);
-      nchunks += c1 - c0;
-      ++nseg;
-      cur += c1 - c0;
-    }
-    st->nseg = nseg;
-    st->nchunks = nchunks;
-    st->per = per;
-    st->cpp = cpp;
+    const int P = nb * p.H, base = P / G, rem = P - base * G;
+    st->pair_base = base;
+    st->pair_rem = rem;
+    st->npairs = base + (rank < rem ? 1 : 0);
+    st->pair0 = rank * base + (rank < rem ? rank : rem);
+    st->cpp = (p.S + kXaChunk - 1) / kXaChunk;
     st->stop = 0;
     st->consumed = 0u;
     for (int i = 0; i < kDsMaxStages; ++i) {
@@ -862,9 +830,15 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
     for (int i = tid; i < p_in.n_layers * words; i += kDsThreads)
       reinterpret_cast<unsigned long long*>(ds_smem + DsSmem::kLayers)[i] =
           reinterpret_cast<const unsigned long long*>(p_in.layers)[i];
+    // operand tiles start out zero: rows >= n_clips are never written, and the MMAs read all 16
+    const int z0 = DsSmem::kTok, z1 = DsSmem::ring(p_in.d);
+    for (int i = z0 + tid * 16; i < z1; i += kDsThreads * 16) {
+      if (i >= DsSmem::kLayers && i < DsSmem::kMisc) continue;
+      *reinterpret_cast<uint4*>(ds_smem + i) = make_uint4(0u, 0u, 0u, 0u);
+    }
   }
   __syncthreads();
-  // every CTA's barriers exist before any peer arrives on them
+  // every CTA's barriers and tiles exist before any peer arrives on / pushes into them
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 
   unsigned issued = 0;
@@ -876,42 +850,36 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
     unsigned cphase = 0;
     DsRing rg;
     rg.cons = 0; rg.slot = 0; rg.par = 0;
-    if (tid == 0) {
-      for (int b = rank; b < B; b += G) {
-        p.lens[p.clip0 + b] = p.prompt_len;
-        p.done[p.clip0 + b] = 0;
-      }
+    float2 xr[2][2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) xr[i][0] = xr[i][1] = make_float2(0.0f, 0.0f);
+    if (rank == 0 && tid < B) {
+      p.lens[p.clip0 + tid] = p.prompt_len;
+      p.done[p.clip0 + tid] = 0;
     }
-    ds_embed(p, 0);
-    ds_cluster_sync(ds_smem, p, cphase, 0, tlast);
     for (int pos = 0; pos <= p.max_total - 2; ++pos) {
+      ds_embed(ds_smem, p, pos, xr);
+      ds_cluster_sync(ds_smem, p, cphase, 10, tlast);
       for (int l = 0; l < p.n_layers; ++l) {
-        const DsLayerDev& L = p.layers[l];
-        ds_gemm(ds_smem, p, rg, DS_QKV, l, pos);    // 1. LN1 -> QKV; q -> qs, k/v -> cache row `pos`
-        ds_cluster_sync(ds_smem, p, cphase, 1, tlast);
-        ds_self_attn(ds_smem, p, L, pos);           // 2. self-attention over cache rows 0..pos
-        ds_cluster_sync(ds_smem, p, cphase, 2, tlast);
-        ds_gemm(ds_smem, p, rg, DS_OUT, l, pos);    // 3. out-proj + residual
-        ds_cluster_sync(ds_smem, p, cphase, 3, tlast);
-        ds_gemm(ds_smem, p, rg, DS_XQ, l, pos);     // 4. LNx -> cross-attention query
-        ds_cluster_sync(ds_smem, p, cphase, 4, tlast);
-        ds_cross_attn(ds_smem, p, rg);              // 5. cross-attention over this CTA's K/V range
-        ds_cluster_sync(ds_smem, p, cphase, 5, tlast);
-        ds_gemm(ds_smem, p, rg, DS_XOUT, l, pos);   // 6. merge of the partials -> out-proj + residual
-        ds_cluster_sync(ds_smem, p, cphase, 6, tlast);
-        ds_gemm(ds_smem, p, rg, DS_FC1, l, pos);    // 7. LN2 -> fc1 -> GELU
-        ds_cluster_sync(ds_smem, p, cphase, 7, tlast);
-        ds_gemm(ds_smem, p, rg, DS_FC2, l, pos);    // 8. fc2 + residual
-        ds_cluster_sync(ds_smem, p, cphase, 8, tlast);
+        // phases 1..8: QKV, self-attention, out-proj, cross query, cross-attention, cross out-proj, fc1, fc2
+#pragma unroll 1
+        for (int ph = 1; ph <= 8; ++ph) {
+          if (ph == 2) {
+            ds_self_attn(ds_smem, p, p.layers[l], pos);
+          } else if (ph == 5) {
+            ds_cross_attn(ds_smem, p, rg);
+          } else {
+            const int kind = ph == 1 ? DS_QKV : ph == 3 ? DS_OUT : ph == 4 ? DS_XQ : ph == 6 ? DS_XOUT : ph == 7 ? DS_FC1 : DS_FC2;
+            ds_gemm(ds_smem, p, rg, kind, l, pos, xr);
+          }
+          ds_cluster_sync(ds_smem, p, cphase, ph, tlast);
+        }
       }
       if (pos >= p.prompt_len - 1) {
         ds_logits(ds_smem, p, rg, pos);
         ds_cluster_sync(ds_smem, p, cphase, 9, tlast);
-        ds_finalize(ds_smem, p, pos);
+        if (ds_finalize(ds_smem, p, pos) >= B) break;  // every clip has produced EOT (whisper.cpp:397-399, per clip)
       }
-      if (pos + 1 <= p.max_total - 2) ds_embed(p, pos + 1);
-      ds_cluster_sync(ds_smem, p, cphase, 10, tlast);
-      if (__ldcg(p.finished) >= B) break;  // every clip has produced EOT (whisper.cpp:397-399, per clip)
     }
     if (tid == 0) {
       DsStream* st = ds_stream(ds_smem);

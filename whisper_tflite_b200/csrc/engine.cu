@@ -914,25 +914,16 @@ int wt_engine::decode_persistent(int n_clips, int prompt_len, int max_total, int
     q.pos_emb = (const bf16*)dec_pos;
     q.tokens = tokens; q.lens = lens; q.done = done;
     q.prompt_len = prompt_len; q.max_total = max_total; q.eot = eot;
-    q.x = pd_x; q.qs = pd_qs; q.att = pd_att; q.qx = pd_qx; q.hmid = pd_hmid;
-    q.xpart = pd_xpart;
+    q.qs = pd_qs;
     {
-      int slots = 0;
-      const int last = n_clips - (n_groups - 1) * gsz;
-      const int cand[2] = {n_groups > 1 ? gsz : last, last};
-      const int cpp = (S + wt::kXaChunk - 1) / wt::kXaChunk;
-      for (int i = 0; i < 2; ++i) {
-        const int per = (cand[i] * H * cpp + dec_cluster - 1) / dec_cluster;
-        const int sl = (cpp + per - 1) / per + 1;
-        if (sl > slots) slots = sl;
-      }
-      q.xslots = slots;
+      // whole (clip, head) pairs per CTA and the residual columns per warp must fit their fixed tables
+      const int pairs = ((gsz < n_clips ? gsz : n_clips) * H + dec_cluster - 1) / dec_cluster;
+      const int res_groups = (d / 8 + dec_cluster - 1) / dec_cluster;
+      if (pairs > wt::kDsMaxSeg || res_groups > 16)
+        return fail(WT_ERR_STATE, "streaming decoder: %d pairs / %d residual groups per CTA exceed the kernel's tables (cluster %d)", pairs, res_groups, dec_cluster);
     }
-    if (q.xslots > pd_xslots_cap) return fail(WT_ERR_STATE, "cross-attention partial slots %d exceed capacity %d", q.xslots, pd_xslots_cap);
-    q.amax_part = pd_amax;
     q.step_logits = keep_logits ? step_logits : nullptr;
     q.step_logits_stride = (long long)max_batch * dims.n_vocab;
-    q.finished = pd_finished;
     q.trace = pd_trace;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(n_groups * dec_cluster);
