@@ -292,9 +292,20 @@ def run_gpu(args):
                 ach = byt / sec / 1e9
                 return {"kernel": "decode_cross_attn_kernel", "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"],
                         "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": None}
+            if name == "dec_persistent":
+                # one launch = the whole greedy loop: per position, every layer streams each clip's cross K/V
+                # (B * 2 * 1500 * d bf16) and the layer's projection weights (14 d^2 bf16) once; the tied logits matrix
+                # (V * d bf16) once per generated token
+                dm = synth.DIMS[MODEL]
+                d, L, V = dm.d_model, dm.n_dec_layers, dm.n_vocab
+                n_pos, n_gen = capi.MAX_TOKENS - 1, capi.MAX_TOKENS - len(capi.REFERENCE_PROMPT)
+                byt = (n_pos * L * (B * 2 * 1500 * d * 2 + 14 * d * d * 2) + n_gen * V * d * 2) * st["launches_per_step"]
+                ach = byt / sec / 1e9
+                return {"kernel": "decoder_stream_kernel (persistent greedy loop)", "bound": "hbm", "achieved": ach,
+                        "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": None}
             return None
 
-        roofs = {k: roof(k) for k in ("mel_frames", "enc_gemm", "enc_attention", "dec_cross_attn")}
+        roofs = {k: roof(k) for k in ("mel_frames", "enc_gemm", "enc_attention", "dec_cross_attn", "dec_persistent")}
         roofline = roofs.get(dom) or roofs["enc_gemm"] or {}
         roofline = dict(roofline)
         roofline["dominant_stage"] = dom

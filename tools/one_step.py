@@ -16,10 +16,11 @@ size = sys.argv[2] if len(sys.argv) > 2 else "tiny"
 B = int(sys.argv[3]) if len(sys.argv) > 3 else 64
 bench.MODEL = size
 eng = capi.Engine(bench.ensure_weights(size), max_batch=B)
+init_launches = eng.launch_count
 pcm = torch.from_numpy(synth.synth_pcm(B, seed=0)).cuda()
 ids = torch.empty(B, 31, dtype=torch.int32, device="cuda")
 lens = torch.empty(B, dtype=torch.int32, device="cuda")
 for _ in range(n):
     eng.transcribe_tokens(pcm, ids_out=ids, lens_out=lens)
 eng.synchronize()
-print("lens", lens[:4].tolist(), "launches", eng.launch_count)
+print("lens", lens[:4].tolist(), "launches", eng.launch_count - init_launches, "init", init_launches)

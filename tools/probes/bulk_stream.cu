@@ -78,8 +78,8 @@ int main() {
   cudaEvent_t a, b;
   cudaEventCreate(&a);
   cudaEventCreate(&b);
-  const int ctas_list[3] = {112, 148, 296};
-  for (int ci = 0; ci < 3; ++ci) {
+  const int ctas_list[4] = {16, 48, 112, 148};
+  for (int ci = 0; ci < 4; ++ci) {
     const int ctas = ctas_list[ci];
     const size_t per_cta = ((total / ctas) / (64 * 1024)) * (64 * 1024);
     for (int chunk = 8192; chunk <= 65536; chunk *= 2) {

@@ -39,7 +39,7 @@ def build_cuda(force: bool = False, verbose: bool = False) -> str:
     deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h"))]
     deps.append(os.path.join(os.path.dirname(HERE), "include", "whisper_b200.h"))
     if force or _newer(LIB, deps):
-        cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
+        cmd = [_nvcc()] + NVCC_FLAGS + os.environ.get("WT_NVCC_EXTRA", "").split() + (["-Xptxas", "-v"] if verbose else []) + \
               ["-o", LIB, os.path.join(CSRC, "engine.cu"), "-lcudart"]
         subprocess.check_call(cmd)
     return LIB

@@ -198,7 +198,7 @@ class Engine:
     def decoder_trace(self, reset: bool = True):
         """WT_DEC_TRACE=1 engines: {phase: (total us, barrier-wait us)} of the persistent decoder as seen by CTA 0."""
         names = ["init", "ln1_qkv", "self_attn", "out_proj", "lnx_xq", "cross_attn", "xout_proj", "ln2_fc1", "fc2",
-                 "logits", "finalize_embed", "gemm:w_issue", "gemm:stage", "gemm:mma", "gemm:epilogue", "dbg:repeat_xq"]
+                 "logits", "finalize_embed", "gemm:norm", "gemm:mma", "gemm:epilogue", "sync:fence", "sync:bar+arrive"]
         buf = (ctypes.c_uint64 * 32)()
         _check(self.lib.wt_debug_decoder_trace(self.h, buf, int(reset)))
         return {n: (buf[i] / 1e3, buf[16 + i] / 1e3) for i, n in enumerate(names)}

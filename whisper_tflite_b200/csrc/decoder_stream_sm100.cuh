@@ -23,6 +23,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#ifndef DS_TRACE_FINE
+#define DS_TRACE_FINE 0
+#endif
 #include "decoder_sm100.cuh"  // shared small helpers (mma wrapper, bf16 unpack, ex2, globaltimer, cluster ids)
 
 namespace wt {
@@ -36,6 +39,16 @@ constexpr int kDsMaxStages = 6;
 constexpr int kDsMaxSeg = 24;                     // (clip, head) pairs one CTA may own
 constexpr int kDsMaxLayers = 12;
 constexpr int kDsUnitBytes = 512;                // one (8-column group, 32-wide k block) weight unit: 32 lanes x 16 B
+
+// weight units per warp and ring stage of a round with `nact` active warps: the largest divisor of the group's k blocks
+// that keeps the stage (nact * upw units of 512 B) within kDsStageBytes — as few, as large bulk copies as possible
+// (measured: <= 4 bulk copies in flight per SM at ~1.3 us each, whatever their size; tools/probes/bulk_stream.cu)
+__host__ __device__ inline int ds_upw(int kbK, int nact) {
+  const int cap = (kDsStageBytes / kDsUnitBytes) / nact;
+  for (int u = (cap < kbK ? cap : kbK); u > 1; --u)
+    if (kbK % u == 0) return u;
+  return 1;
+}
 
 enum : int { DS_QKV = 0, DS_OUT = 1, DS_XQ = 2, DS_XOUT = 3, DS_FC1 = 4, DS_FC2 = 5, DS_LOGITS = 6, DS_NKIND = 7 };
 
@@ -72,7 +85,9 @@ struct DsParams {
 struct DsStream {
   long long slice_unit0[DS_NKIND];  // first weight unit of this CTA's slice, per kind
   int ng[DS_NKIND];                 // 8-column groups owned by this CTA
-  int kph[DS_NKIND];                // ring stages per group = (K / 32) / upw
+  int kbk[DS_NKIND];                // 32-wide k blocks per group (K / 32)
+  int upw_full[DS_NKIND];           // ds_upw of a full round (8 active warps) and of the slice's last, partial round
+  int upw_last[DS_NKIND];
   int pair0, npairs;                // cross-attention: whole (clip, head) pairs [pair0, pair0 + npairs) of the group
   int pair_base, pair_rem;          // balanced split of the group's pairs over the cluster
   int cpp;                          // K/V chunks per pair
@@ -170,12 +185,22 @@ __device__ __forceinline__ void ds_cluster_sync(uint8_t* smem, const DsParams& p
   const bool tr = p.trace != nullptr && threadIdx.x == 0;
   const unsigned long long t_arr = tr ? dec_globaltimer() : 0ull;
   asm volatile("fence.acq_rel.cluster;" ::: "memory");
+#if DS_TRACE_FINE
+  const unsigned long long t_f = tr ? dec_globaltimer() : 0ull;
+#endif
   ds_cons_bar();
   const uint32_t local = smem_u32(ds_cbar(smem));
   if (threadIdx.x < (unsigned)p.G) {
     const uint32_t remote = ds_mapa(local, (int)threadIdx.x);
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
   }
+#if DS_TRACE_FINE
+  if (tr) {
+    const unsigned long long t_b = dec_globaltimer();
+    atomicAdd(p.trace + 14, t_f - t_arr);
+    atomicAdd(p.trace + 15, t_b - t_f);
+  }
+#endif
   asm volatile(
       "{\n\t.reg .pred P1;\n\t"
       "DS_CW_LOOP:\n\t"
@@ -203,7 +228,7 @@ __device__ __forceinline__ void ds_cluster_sync(uint8_t* smem, const DsParams& p
 // w * upw * 512.
 // ---------------------------------------------------------------------------------------------------
 __global__ void ds_pack_weights_kernel(const __nv_bfloat16* __restrict__ W, const float* __restrict__ gamma,
-                                       uint4* __restrict__ out, int N, int K, int G, int upw) {
+                                       uint4* __restrict__ out, int N, int K, int G) {
   const int n_groups = (N + 7) >> 3, kbK = K >> 5, gpc = (n_groups + G - 1) / G;
   const long long total = (long long)n_groups * kbK * 32;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
@@ -215,6 +240,7 @@ __global__ void ds_pack_weights_kernel(const __nv_bfloat16* __restrict__ W, cons
     const int ng_r = (n_groups - r * gpc < gpc) ? n_groups - r * gpc : gpc;
     const int rho = gl >> 3, w = gl & 7;
     const int nact = (ng_r - 8 * rho < 8) ? ng_r - 8 * rho : 8;
+    const int upw = ds_upw(kbK, nact);
     const int h = kb / upw, u = kb - h * upw;
     const long long unit = (long long)r * gpc * kbK + (long long)rho * 8 * kbK + (long long)h * nact * upw + w * upw + u;
     const int n = g * 8 + (lane >> 2), k0 = kb * 32 + (lane & 3) * 8;
@@ -297,9 +323,10 @@ struct DsRing {
 // One 8-column group per warp and round, accumulated over kph ring stages of upw units (2 MMAs each, two independent
 // accumulator chains). Returns with the warp's 16 x 8 tile in acc (rows g / g+8, columns 2t, 2t+1 of the group).
 __device__ __forceinline__ void ds_mma_round(uint8_t* smem, const DsParams& p, DsRing& rg, const uint8_t* ring,
-                                             const uint8_t* a_lane, int as, int kph, bool active, float (&acc)[4]) {
+                                             const uint8_t* a_lane, int as, int upw, int kph, int nact,
+                                             float (&acc)[4]) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int upw = p.upw;
+  const bool active = warp < nact;
   uint64_t* full = ds_full(smem);
   uint64_t* empty = ds_empty(smem);
   float a0[4] = {0.0f, 0.0f, 0.0f, 0.0f}, a1[4] = {0.0f, 0.0f, 0.0f, 0.0f};
@@ -334,15 +361,23 @@ __device__ __forceinline__ void ds_gemm(uint8_t* smem, const DsParams& p, DsRing
   const DsStream* st = ds_stream(smem);
   const int d = p.d, B = p.n_clips, G = p.G;
   const bool from_h = kind == DS_FC2;
+#if DS_TRACE_FINE
+  const bool tr = p.trace != nullptr && threadIdx.x == 0;
+#else
+  constexpr bool tr = false;
+#endif
+  unsigned long long tm = tr ? dec_globaltimer() : 0ull;
   if (kind == DS_QKV || kind == DS_XQ || kind == DS_FC1) {
     ds_stage_norm(smem, B, d);
     ds_cons_bar();
   }
+  if (tr) { const unsigned long long t_ = dec_globaltimer(); atomicAdd(p.trace + 11, t_ - tm); tm = t_; }
   const int as = from_h ? DsSmem::h_stride(d) : DsSmem::a_stride(d);
   const uint8_t* sA = smem + (from_h ? DsSmem::h_off(d) : DsSmem::a_off(d));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-  const int ng = st->ng[kind], kph = st->kph[kind];
-  const int g0 = (int)(st->slice_unit0[kind] / (kph * p.upw));  // first group of this CTA's slice
+  const int ng = st->ng[kind], kbK = st->kbk[kind];
+  const int g0 = (int)(st->slice_unit0[kind] / kbK);  // first group of this CTA's slice
+  const int upw_f = st->upw_full[kind], upw_l = st->upw_last[kind], kph_f = kbK / upw_f, kph_l = kbK / upw_l;
   const float* bias = L.b[kind];
   const uint8_t* ring = smem + DsSmem::ring(d);
   const uint8_t* a_lane = sA + (size_t)g * as + t * 16;
@@ -353,7 +388,12 @@ __device__ __forceinline__ void ds_gemm(uint8_t* smem, const DsParams& p, DsRing
     float2 bz = make_float2(0.0f, 0.0f);
     if (active) bz = __ldg(reinterpret_cast<const float2*>(bias + n));
     float acc[4];
-    ds_mma_round(smem, p, rg, ring, a_lane, as, kph, active, acc);
+    {
+      const int nact = (ng - rho * 8 < 8) ? ng - rho * 8 : 8;
+      const int upw = nact == 8 ? upw_f : upw_l;
+      ds_mma_round(smem, p, rg, ring, a_lane, as, upw, nact == 8 ? kph_f : kph_l, nact, acc);
+    }
+    if (tr) { const unsigned long long t_ = dec_globaltimer(); atomicAdd(p.trace + 12, t_ - tm); tm = t_; }
     if (!active) continue;
     const float v00 = acc[0] + bz.x, v01 = acc[1] + bz.y, v10 = acc[2] + bz.x, v11 = acc[3] + bz.y;
     switch (kind) {
@@ -404,6 +444,7 @@ __device__ __forceinline__ void ds_gemm(uint8_t* smem, const DsParams& p, DsRing
         break;
       }
     }
+    if (tr) { const unsigned long long t_ = dec_globaltimer(); atomicAdd(p.trace + 13, t_ - tm); tm = t_; }
   }
 }
 
@@ -413,7 +454,7 @@ __device__ __forceinline__ void ds_embed(uint8_t* smem, const DsParams& p, int p
   const int d = p.d, B = p.n_clips, G = p.G;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int ng = st->ng[DS_OUT];
-  const int g0 = (int)(st->slice_unit0[DS_OUT] / (st->kph[DS_OUT] * p.upw));
+  const int g0 = (int)(st->slice_unit0[DS_OUT] / st->kbk[DS_OUT]);
   const int* s_tok = ds_tok(smem);
   const uint32_t sxb = smem_u32(smem + DsSmem::kX);
   const int xs = DsSmem::x_stride(d);
@@ -447,8 +488,9 @@ __device__ __noinline__ void ds_logits(uint8_t* smem, const DsParams& p, DsRing&
   if (tid < kDsRows) s_best[tid] = 0ull;
   ds_stage_norm(smem, B, d);
   ds_cons_bar();
-  const int ng = st->ng[DS_LOGITS], kph = st->kph[DS_LOGITS];
-  const int g0 = (int)(st->slice_unit0[DS_LOGITS] / (kph * p.upw));
+  const int ng = st->ng[DS_LOGITS], kbK = st->kbk[DS_LOGITS];
+  const int g0 = (int)(st->slice_unit0[DS_LOGITS] / kbK);
+  const int upw_f = st->upw_full[DS_LOGITS], upw_l = st->upw_last[DS_LOGITS], kph_f = kbK / upw_f, kph_l = kbK / upw_l;
   const uint8_t* ring = smem + DsSmem::ring(d);
   const uint8_t* a_lane = sA + (size_t)g * as + t * 16;
   const int step = pos - (p.prompt_len - 1);
@@ -461,7 +503,10 @@ __device__ __noinline__ void ds_logits(uint8_t* smem, const DsParams& p, DsRing&
     float2 bz = make_float2(0.0f, 0.0f);
     if (active) bz = __ldg(reinterpret_cast<const float2*>(p.b_logits + n));  // padded to a multiple of 8 on the host
     float acc[4];
-    ds_mma_round(smem, p, rg, ring, a_lane, as, kph, active, acc);
+    {
+      const int nact = (ng - rho * 8 < 8) ? ng - rho * 8 : 8;
+      ds_mma_round(smem, p, rg, ring, a_lane, as, nact == 8 ? upw_f : upw_l, nact == 8 ? kph_f : kph_l, nact, acc);
+    }
     if (!active) continue;
     const float v00 = acc[0] + bz.x, v01 = acc[1] + bz.y, v10 = acc[2] + bz.x, v11 = acc[3] + bz.y;
     if (n < V) {
@@ -727,11 +772,12 @@ struct DsProd {
     if (++slot == n_stages) { slot = 0; par ^= 1u; }
     return true;
   }
-  __device__ __forceinline__ bool weights(const uint4* base, int kind, int upw, uint64_t policy) {
-    const int ng = st->ng[kind], kph = st->kph[kind];
+  __device__ __forceinline__ bool weights(const uint4* base, int kind, uint64_t policy) {
+    const int ng = st->ng[kind], kbK = st->kbk[kind];
     const uint4* src = base + st->slice_unit0[kind] * 32;
     for (int rho = 0; rho * 8 < ng; ++rho) {
       const int nact = (ng - rho * 8 < 8) ? ng - rho * 8 : 8;
+      const int upw = nact == 8 ? st->upw_full[kind] : st->upw_last[kind], kph = kbK / upw;
       const uint32_t bytes = (uint32_t)(nact * upw * kDsUnitBytes);
       for (int h = 0; h < kph; ++h) {
         if (!issue(src, bytes, policy)) return false;
@@ -750,25 +796,25 @@ __device__ __noinline__ unsigned ds_producer(uint8_t* smem, const DsParams& p) {
   pr.st = ds_stream(smem);
   pr.n = 0; pr.slot = 0; pr.par = 0; pr.n_stages = p.n_stages;
   const uint64_t pol_kv = l2_evict_first_policy(), pol_w = l2_evict_last_policy();
-  const int pair0 = pr.st->pair0, npairs = pr.st->npairs, cpp = pr.st->cpp, upw = p.upw;
+  const int pair0 = pr.st->pair0, npairs = pr.st->npairs, cpp = pr.st->cpp;
   const size_t chunk_elems = (size_t)2 * kXaChunk * 64;
   for (int pos = 0; pos <= p.max_total - 2; ++pos) {
     for (int l = 0; l < p.n_layers; ++l) {
       const DsLayerDev& L = p.layers[l];
-      if (!pr.weights(L.w[DS_QKV], DS_QKV, upw, pol_w)) return pr.n;
-      if (!pr.weights(L.w[DS_OUT], DS_OUT, upw, pol_w)) return pr.n;
-      if (!pr.weights(L.w[DS_XQ], DS_XQ, upw, pol_w)) return pr.n;
+      if (!pr.weights(L.w[DS_QKV], DS_QKV, pol_w)) return pr.n;
+      if (!pr.weights(L.w[DS_OUT], DS_OUT, pol_w)) return pr.n;
+      if (!pr.weights(L.w[DS_XQ], DS_XQ, pol_w)) return pr.n;
       {
         const __nv_bfloat16* src = L.kvx + ((size_t)p.clip0 * p.H + pair0) * cpp * chunk_elems;
         for (int c = 0; c < npairs * cpp; ++c, src += chunk_elems)
           if (!pr.issue(src, (uint32_t)kDsStageBytes, pol_kv)) return pr.n;
       }
-      if (!pr.weights(L.w[DS_XOUT], DS_XOUT, upw, pol_w)) return pr.n;
-      if (!pr.weights(L.w[DS_FC1], DS_FC1, upw, pol_w)) return pr.n;
-      if (!pr.weights(L.w[DS_FC2], DS_FC2, upw, pol_w)) return pr.n;
+      if (!pr.weights(L.w[DS_XOUT], DS_XOUT, pol_w)) return pr.n;
+      if (!pr.weights(L.w[DS_FC1], DS_FC1, pol_w)) return pr.n;
+      if (!pr.weights(L.w[DS_FC2], DS_FC2, pol_w)) return pr.n;
     }
     if (pos >= p.prompt_len - 1)
-      if (!pr.weights(p.w_logits, DS_LOGITS, upw, pol_w)) return pr.n;
+      if (!pr.weights(p.w_logits, DS_LOGITS, pol_w)) return pr.n;
   }
   return pr.n;
 }
@@ -807,7 +853,9 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
       int ng = n_groups - rank * gpc;
       ng = ng < 0 ? 0 : (ng > gpc ? gpc : ng);
       st->ng[k] = ng;
-      st->kph[k] = kbK / p.upw;
+      st->kbk[k] = kbK;
+      st->upw_full[k] = ds_upw(kbK, 8);
+      st->upw_last[k] = (ng & 7) ? ds_upw(kbK, ng & 7) : ds_upw(kbK, 8);
       st->slice_unit0[k] = (long long)rank * gpc * kbK;
     }
     const int P = nb * p.H, base = P / G, rem = P - base * G;

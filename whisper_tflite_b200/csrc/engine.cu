@@ -854,9 +854,10 @@ int wt_engine::init_stream_weights() {
     WT_TRY(alloc(&pb, (size_t)n_groups * 8, true));
     const long long total = (long long)n_groups * kbK * 32;
     const int blocks = (int)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096);
-    wt::ds_pack_weights_kernel<<<blocks, 256, 0, stream>>>((const bf16*)lin.w, ln ? ln->g : nullptr, pw, lin.N, lin.K, G, ds_upw);
+    wt::ds_pack_weights_kernel<<<blocks, 256, 0, stream>>>((const bf16*)lin.w, ln ? ln->g : nullptr, pw, lin.N, lin.K, G);
     wt::ds_fold_bias_kernel<<<(lin.N * 32 + 255) / 256, 256, 0, stream>>>((const bf16*)lin.w, lin.b, ln ? ln->b : nullptr, pb, lin.N, lin.K);
     WT_CUDA_OK(cudaGetLastError());
+    launches += 2;
     *w_out = pw;
     *b_out = pb;
     return WT_OK;
