@@ -33,7 +33,8 @@ namespace wt {
 
 constexpr int kGemmBM = 128;
 constexpr int kGemmBK = 64;
-constexpr int kGemmThreads = 192;
+constexpr int kGemmEpiGroups = 2;   // epilogue warp groups (4 warps each): group e drains the accumulator stage of tiles it & 1 == e
+constexpr int kGemmThreads = 64 + kGemmEpiGroups * 128;
 
 enum : int { EPI_ADD = 4, EPI_OUT_F32 = 16, EPI_ARGMAX = 32, EPI_SPLIT_KV = 64 };  // EPI_BIAS = 1, EPI_GELU = 2 shared with SIMT
 
@@ -193,12 +194,12 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 
 template <int BN>
 struct GemmSmem {
-  static constexpr int kStages = (BN <= 128) ? 6 : 4;
+  static constexpr int kStages = (BN <= 64) ? 6 : (BN <= 128) ? 5 : (BN <= 192) ? 4 : 3;
   static constexpr int kABytes = kGemmBM * kGemmBK * 2;  // 16 KB
   static constexpr int kBBytes = BN * kGemmBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kScratchRowBytes = 128 + 16;  // 64 bf16 or 32 f32 per row + pad (keeps 16B phases conflict-free)
-  static constexpr int kScratchBytes = 4 * 32 * kScratchRowBytes;
+  static constexpr int kScratchBytes = kGemmEpiGroups * 4 * 32 * kScratchRowBytes;
   static constexpr int kBiasBytes = 2 * BN * 4;
   static constexpr int kBarBytes = (2 * kStages + 4) * 8 + 16;
   static constexpr int kTotal = kStages * kStageBytes + kScratchBytes + kBiasBytes + kBarBytes + 1024;
@@ -298,14 +299,16 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
       }
     }
   } else {
-    // ================= epilogue (warps 2..5) =================
-    const int ew = warp - 2;            // 0..3 (scratch slot)
+    // ================= epilogue (warps 2..9: two groups of four, one accumulator stage each) =================
+    const int ew = warp - 2;            // 0..7 (scratch slot)
+    const int eg = ew >> 2;             // epilogue group: drains tiles with (it & 1) == eg
     const int lane_q = warp & 3;        // TMEM lane quarter this warp may touch: lanes 32*(warp%4)..+31
-    const int et = threadIdx.x - 64;    // 0..127
+    const int et = (threadIdx.x - 64) & 127;  // 0..127 within the group
     uint8_t* scr = s_scratch + ew * 32 * S::kScratchRowBytes;
     int it = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const int acc = it & 1;
+      if (acc != eg) continue;
       const uint32_t acc_phase = (it >> 1) & 1;
       const int tn = tile % p.n_tiles_n, tm = tile / p.n_tiles_n;
       const int batch = tm / p.tiles_per_batch, row0 = (tm % p.tiles_per_batch) * kGemmBM;
@@ -313,7 +316,7 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
       float* bias_s = s_bias + acc * BN;
       if (p.flags & EPI_BIAS)
         for (int i = et; i < BN; i += 128) bias_s[i] = (n0 + i < p.N) ? __ldg(p.bias + n0 + i) : 0.0f;
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync %0, 128;" ::"r"(1 + eg) : "memory");
       mbar_wait(bar_tfull + acc, acc_phase);
       tc_fence_after();
       const int r_in_tile = lane_q * 32 + lane;           // accumulator row owned by this thread
@@ -322,6 +325,9 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
       const int m = batch * p.rows_per_batch + r_batch;   // logical GEMM row
       const uint32_t t_row = tmem_base + ((uint32_t)(lane_q * 32) << 16) + acc * BN;
       unsigned long long best = 0ull;
+      // a tile never straddles a batch: one RowMap division per tile, rows are then row_stride apart
+      const long long c_base = p.cmap.at(batch * p.rows_per_batch + row0);
+      const long long a_base = (p.flags & EPI_ADD) ? p.add_map.at(batch * p.rows_per_batch + row0) : 0ll;
 
       for (int c0 = 0; c0 < BN; c0 += 32) {
         uint32_t v[32];
@@ -336,7 +342,7 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
         }
         if (p.flags & EPI_GELU) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
+          for (int j = 0; j < 32; ++j) f[j] = gelu_erf_fast(f[j]);
         }
         if (p.flags & EPI_ADD) {
           // coalesced fetch of this warp's 32 rows x 32 cols of the addend through the scratch
@@ -349,7 +355,7 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
             const int col = n0 + c0 + pc * 8;
             uint4 val = make_uint4(0u, 0u, 0u, 0u);
             if (rb < p.rows_per_batch && col < p.N)
-              val = *reinterpret_cast<const uint4*>(p.addend + p.add_map.at(batch * p.rows_per_batch + rb) + col);
+              val = *reinterpret_cast<const uint4*>(p.addend + a_base + (long long)(rb - row0) * p.add_map.row_stride + col);
             *reinterpret_cast<uint4*>(scr + rr * S::kScratchRowBytes + pc * 16) = val;
           }
           __syncwarp();
@@ -389,7 +395,7 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
             const int col = n0 + c0 + pc * 4;
             if (rb < p.rows_per_batch && col < p.N) {
               const float4 val = *reinterpret_cast<const float4*>(scr + rr * S::kScratchRowBytes + pc * 16);
-              float* dst = reinterpret_cast<float*>(p.C) + p.cmap.at(batch * p.rows_per_batch + rb) + col;
+              float* dst = reinterpret_cast<float*>(p.C) + c_base + (long long)(rb - row0) * p.cmap.row_stride + col;
               if (col + 3 < p.N && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
                 *reinterpret_cast<float4*>(dst) = val;
               } else {
@@ -431,8 +437,8 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
                 }
                 *reinterpret_cast<uint4*>(dst) = val;
               } else {
-                *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C) +
-                                          p.cmap.at(batch * p.rows_per_batch + rb) + col) = val;
+                *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C) + c_base +
+                                          (long long)(rb - row0) * p.cmap.row_stride + col) = val;
               }
             }
           }

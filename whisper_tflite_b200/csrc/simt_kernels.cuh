@@ -22,6 +22,20 @@ template <> __device__ __forceinline__ float from_f32<float>(float v) { return v
 template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16(v); }
 
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+// Same function for the bf16 epilogues: erf by Abramowitz & Stegun 7.1.26 (|error| <= 1.5e-7, far below one bf16 ulp of
+// the result) — one reciprocal, one ex2 and a 5-term Horner instead of erff's branches.
+__device__ __forceinline__ float gelu_erf_fast(float x) {
+  const float z = fabsf(x) * 0.70710678118654752f;
+  const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
+  float y = fmaf(1.061405429f, t, -1.453152027f);
+  y = fmaf(y, t, 1.421413741f);
+  y = fmaf(y, t, -0.284496736f);
+  y = fmaf(y, t, 0.254829592f);
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-z * z * 1.4426950408889634f));
+  const float c = 0.5f * y * t * e;                 // 0.5 erfc(|x| / sqrt 2) = Phi(-|x|)
+  return x * (x < 0.0f ? c : 1.0f - c);             // x Phi(x), no cancellation in the negative tail
+}
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
