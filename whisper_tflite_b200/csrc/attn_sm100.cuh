@@ -162,36 +162,44 @@ attention_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
       tc_fence_after();
       const uint32_t t_s = tmem_s + lane_sel + (j & 1) * 128;
       const int valid = S - j * 128;  // keys valid in this block (>= 128 except the last)
-      // pass 1: row max
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld32(t_s + c * 32, v);
-        tmem_ld_wait();
+      // the whole S row (128 f32) in registers with ONE wait: the four loads are in flight together
+      uint32_t sv[128];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) tmem_ld32(t_s + c * 32, sv + c * 32);
+      tmem_ld_wait();
+      // row max: four independent chains; only the clip's last key block carries a mask
+      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+      if (valid >= 128) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          const float s = __uint_as_float(v[i]);
-          mx = fmaxf(mx, (c * 32 + i < valid) ? s : -INFINITY);
+          mx0 = fmaxf(mx0, __uint_as_float(sv[i]));
+          mx1 = fmaxf(mx1, __uint_as_float(sv[32 + i]));
+          mx2 = fmaxf(mx2, __uint_as_float(sv[64 + i]));
+          mx3 = fmaxf(mx3, __uint_as_float(sv[96 + i]));
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 128; ++i) {
+          if (i >= valid) sv[i] = 0xff800000u;  // -inf: exp2 -> 0, never the maximum
+          mx0 = fmaxf(mx0, __uint_as_float(sv[i]));
         }
       }
+      const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
       const float m_new = fmaxf(m_run, mx * c_scale);
       const float alpha = ex2_approx(m_run - m_new);
-      // pass 2: P = exp2(s*c - m), row sum, bf16 -> swizzled shared tile
-      float l_blk = 0.0f;
+      // P = exp2(s*c - m), row sum (four chains), bf16 -> swizzled shared tile
+      float l0 = 0.0f, l1 = 0.0f, l2 = 0.0f, l3 = 0.0f;
       uint8_t* p_row = p_row_base + (j & 1) * 2 * kAtTile;
-#pragma unroll 1
+#pragma unroll
       for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld32(t_s + c * 32, v);
-        tmem_ld_wait();
         float pv[32];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const float t = fmaf(__uint_as_float(v[i]), c_scale, -m_new);
-          const float e = ex2_approx(t);
-          pv[i] = (c * 32 + i < valid) ? e : 0.0f;
-          l_blk += pv[i];
+        for (int i = 0; i < 32; i += 4) {
+          pv[i] = ex2_approx(fmaf(__uint_as_float(sv[c * 32 + i]), c_scale, -m_new));
+          pv[i + 1] = ex2_approx(fmaf(__uint_as_float(sv[c * 32 + i + 1]), c_scale, -m_new));
+          pv[i + 2] = ex2_approx(fmaf(__uint_as_float(sv[c * 32 + i + 2]), c_scale, -m_new));
+          pv[i + 3] = ex2_approx(fmaf(__uint_as_float(sv[c * 32 + i + 3]), c_scale, -m_new));
+          l0 += pv[i]; l1 += pv[i + 1]; l2 += pv[i + 2]; l3 += pv[i + 3];
         }
         // 32 keys = 4 chunks of 16 bytes; key block c*32 lies in sub-tile c/2, chunk index (c&1)*4 + q
         uint8_t* sub = p_row + (c >> 1) * kAtTile;
@@ -203,6 +211,7 @@ attention_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
                          pack_bf16x2(pv[8 * q + 4], pv[8 * q + 5]), pack_bf16x2(pv[8 * q + 6], pv[8 * q + 7]));
         }
       }
+      const float l_blk = (l0 + l1) + (l2 + l3);
       l_run = l_run * alpha + l_blk;
       m_run = m_new;
       fence_proxy_async();
@@ -215,14 +224,12 @@ attention_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
         mbar_wait(bar_o_full + (jp & 1), (uint32_t)((jp >> 1) & 1));
         tc_fence_after();
         const uint32_t t_o = tmem_o + lane_sel + (jp & 1) * 64;
+        uint32_t v[64];
+        tmem_ld32(t_o, v);
+        tmem_ld32(t_o + 32, v + 32);
+        tmem_ld_wait();
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t v[32];
-          tmem_ld32(t_o + c * 32, v);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o[c * 32 + i] = fmaf(o[c * 32 + i], alpha_prev, __uint_as_float(v[i]));
-        }
+        for (int i = 0; i < 64; ++i) o[i] = fmaf(o[i], alpha_prev, __uint_as_float(v[i]));
       }
       alpha_prev = alpha;
     }
@@ -231,14 +238,12 @@ attention_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
       mbar_wait(bar_o_full + (jp & 1), (uint32_t)((jp >> 1) & 1));
       tc_fence_after();
       const uint32_t t_o = tmem_o + lane_sel + (jp & 1) * 64;
+      uint32_t v[64];
+      tmem_ld32(t_o, v);
+      tmem_ld32(t_o + 32, v + 32);
+      tmem_ld_wait();
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t v[32];
-        tmem_ld32(t_o + c * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[c * 32 + i] = fmaf(o[c * 32 + i], alpha_prev, __uint_as_float(v[i]));
-      }
+      for (int i = 0; i < 64; ++i) o[i] = fmaf(o[i], alpha_prev, __uint_as_float(v[i]));
     }
     const int q = q0 + row;
     if (q < S) {

@@ -502,7 +502,19 @@ int wt_engine::layernorm(const void* in, const LNp& ln, void* out, int rows) {
   pre_launch();
   if (f32mode())
     wt::layernorm_kernel<float, float><<<grid, 256, 0, stream>>>((const float*)in, ln.g, ln.b, (float*)out, rows, D);
-  else
+  else if (D % 128 == 0 && D <= 1024) {
+    // one warp per two rows, 8 warps per block
+    dim3 g2((rows + 15) / 16);
+    const bf16* xi = (const bf16*)in;
+    bf16* yo = (bf16*)out;
+    switch (D / 128) {
+      case 3: wt::layernorm_bf16_vec_kernel<3><<<g2, 256, 0, stream>>>(xi, ln.g, ln.b, yo, rows); break;
+      case 4: wt::layernorm_bf16_vec_kernel<4><<<g2, 256, 0, stream>>>(xi, ln.g, ln.b, yo, rows); break;
+      case 6: wt::layernorm_bf16_vec_kernel<6><<<g2, 256, 0, stream>>>(xi, ln.g, ln.b, yo, rows); break;
+      case 8: wt::layernorm_bf16_vec_kernel<8><<<g2, 256, 0, stream>>>(xi, ln.g, ln.b, yo, rows); break;
+      default: wt::layernorm_kernel<bf16, bf16><<<grid, 256, 0, stream>>>(xi, ln.g, ln.b, yo, rows, D); break;
+    }
+  } else
     wt::layernorm_kernel<bf16, bf16><<<grid, 256, 0, stream>>>((const bf16*)in, ln.g, ln.b, (bf16*)out, rows, D);
   return check_launch("layernorm_kernel");
 }

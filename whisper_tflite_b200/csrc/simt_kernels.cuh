@@ -567,6 +567,76 @@ __global__ void __launch_bounds__(256) mel_to_time_major_kernel(const float* mel
   }
 }
 
+// bf16 rows with D % 128 == 0 (384 / 512 / 768 / 1024): 8-byte loads and stores (256 contiguous bytes per warp access),
+// two rows per warp in flight. HBM-bound: D * 4 bytes per row.
+template <int PER>  // uint2 (4 bf16) per lane and row = D / 128
+__global__ void __launch_bounds__(256) layernorm_bf16_vec_kernel(const __nv_bfloat16* __restrict__ x,
+                                                                  const float* __restrict__ gamma,
+                                                                  const float* __restrict__ beta,
+                                                                  __nv_bfloat16* __restrict__ y, int rows) {
+  constexpr int D = PER * 128;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  const int r0 = warp * 2;
+  if (r0 >= rows) return;
+  const bool two = r0 + 1 < rows;
+  const uint2* xa = reinterpret_cast<const uint2*>(x + (long long)r0 * D);
+  const uint2* xb = reinterpret_cast<const uint2*>(x + (long long)(two ? r0 + 1 : r0) * D);
+  uint2 ra[PER], rb[PER];
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    ra[i] = __ldg(xa + i * 32 + lane);
+    rb[i] = __ldg(xb + i * 32 + lane);
+  }
+  float va[PER][4], vb[PER][4];
+  float sa = 0.0f, sb = 0.0f;
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    va[i][0] = __uint_as_float(ra[i].x << 16); va[i][1] = __uint_as_float(ra[i].x & 0xffff0000u);
+    va[i][2] = __uint_as_float(ra[i].y << 16); va[i][3] = __uint_as_float(ra[i].y & 0xffff0000u);
+    vb[i][0] = __uint_as_float(rb[i].x << 16); vb[i][1] = __uint_as_float(rb[i].x & 0xffff0000u);
+    vb[i][2] = __uint_as_float(rb[i].y << 16); vb[i][3] = __uint_as_float(rb[i].y & 0xffff0000u);
+    sa += (va[i][0] + va[i][1]) + (va[i][2] + va[i][3]);
+    sb += (vb[i][0] + vb[i][1]) + (vb[i][2] + vb[i][3]);
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    sa += __shfl_xor_sync(0xffffffffu, sa, o);
+    sb += __shfl_xor_sync(0xffffffffu, sb, o);
+  }
+  const float ma = sa * (1.0f / D), mb = sb * (1.0f / D);
+  float qa = 0.0f, qb = 0.0f;
+#pragma unroll
+  for (int i = 0; i < PER; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      va[i][j] -= ma;
+      vb[i][j] -= mb;
+      qa = fmaf(va[i][j], va[i][j], qa);
+      qb = fmaf(vb[i][j], vb[i][j], qb);
+    }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    qa += __shfl_xor_sync(0xffffffffu, qa, o);
+    qb += __shfl_xor_sync(0xffffffffu, qb, o);
+  }
+  const float ia = rsqrtf(qa * (1.0f / D) + 1e-5f), ib = rsqrtf(qb * (1.0f / D) + 1e-5f);
+  uint2* ya = reinterpret_cast<uint2*>(y + (long long)r0 * D);
+  uint2* yb = reinterpret_cast<uint2*>(y + (long long)(r0 + 1) * D);
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + i * 32 + lane);
+    const float4 b = __ldg(reinterpret_cast<const float4*>(beta) + i * 32 + lane);
+    __nv_bfloat162 o0 = __floats2bfloat162_rn(va[i][0] * ia * g.x + b.x, va[i][1] * ia * g.y + b.y);
+    __nv_bfloat162 o1 = __floats2bfloat162_rn(va[i][2] * ia * g.z + b.z, va[i][3] * ia * g.w + b.w);
+    ya[i * 32 + lane] = make_uint2(*reinterpret_cast<uint32_t*>(&o0), *reinterpret_cast<uint32_t*>(&o1));
+    if (two) {
+      o0 = __floats2bfloat162_rn(vb[i][0] * ib * g.x + b.x, vb[i][1] * ib * g.y + b.y);
+      o1 = __floats2bfloat162_rn(vb[i][2] * ib * g.z + b.z, vb[i][3] * ib * g.w + b.w);
+      yb[i * 32 + lane] = make_uint2(*reinterpret_cast<uint32_t*>(&o0), *reinterpret_cast<uint32_t*>(&o1));
+    }
+  }
+}
 template <class TI, class TO>
 __global__ void __launch_bounds__(256) convert_kernel(const TI* in, TO* out, long long n) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
