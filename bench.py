@@ -192,37 +192,58 @@ def run_gpu(args):
     wpath = ensure_weights(MODEL)
 
     B = CLIPS_PER_GPU
-    eng = capi.Engine(wpath, device=local, max_batch=B, precision=capi.PRECISION_BF16)
-    # a dedicated (non-default) stream: the engine enqueues on it and the CUDA events below are recorded on it
-    # (wt_set_stream(NULL) would select the engine's own stream, which torch's events cannot see)
-    stream = torch.cuda.Stream()
+    # Serving arrangement (capi.EnginePool): N engines per GPU on separate streams, batches alternate between them, so
+    # one batch's greedy decoder (latency-bound, 4 clusters of 16 clips) runs underneath the next batch's mel + encoder.
+    n_eng = max(1, args.engines)
+    engs = [capi.Engine(wpath, device=local, max_batch=B, precision=capi.PRECISION_BF16) for _ in range(n_eng)]
+    # dedicated (non-default) streams: the engines enqueue on them and the CUDA events below are recorded on them
+    # (wt_set_stream(NULL) would select an engine's own stream, which torch's events cannot see)
+    streams = [torch.cuda.Stream() for _ in range(n_eng)]
+    stream = streams[0]
     torch.cuda.set_stream(stream)
-    assert stream.cuda_stream != 0
-    eng.set_stream(stream.cuda_stream)
-    # every rank gets its own clips (global clip index = rank*B + i), 2 rotating sets so no step re-reads warm inputs
-    sets = [synth.synth_pcm(B, seed=1000 * s + rank) for s in range(2)]
-    d_sets = [torch.from_numpy(p).cuda() for p in sets]
-    h_sets = [torch.from_numpy(p).pin_memory() for p in sets]
-    d_ids = torch.empty(B, capi.MAX_TOKENS, dtype=torch.int32, device="cuda")
-    d_lens = torch.empty(B, dtype=torch.int32, device="cuda")
-    h_ids = torch.empty(B, capi.MAX_TOKENS, dtype=torch.int32).pin_memory()
-    h_lens = torch.empty(B, dtype=torch.int32).pin_memory()
+    for e, st_ in zip(engs, streams):
+        assert st_.cuda_stream != 0
+        e.set_stream(st_.cuda_stream)
+        e.set_decoder_group(16 if n_eng > 1 else 0)
+    eng = engs[0]
+    # every rank gets its own clips (global clip index = rank*B + i), 3 rotating sets so no step re-reads warm inputs
+    n_sets = 3
+    sets = [synth.synth_pcm(B, seed=1000 * s_ + rank) for s_ in range(n_sets)]
+    d_sets = [torch.from_numpy(p_).cuda() for p_ in sets]
+    h_sets = [torch.from_numpy(p_).pin_memory() for p_ in sets]
+    d_ids = [torch.empty(B, capi.MAX_TOKENS, dtype=torch.int32, device="cuda") for _ in range(n_eng)]
+    d_lens = [torch.empty(B, dtype=torch.int32, device="cuda") for _ in range(n_eng)]
+    h_ids = [torch.empty(B, capi.MAX_TOKENS, dtype=torch.int32).pin_memory() for _ in range(n_eng)]
+    h_lens = [torch.empty(B, dtype=torch.int32).pin_memory() for _ in range(n_eng)]
 
     def step_dev(i):
-        eng.transcribe_tokens(d_sets[i & 1], ids_out=d_ids, lens_out=d_lens)
+        j = i % n_eng
+        engs[j].transcribe_tokens(d_sets[i % n_sets], ids_out=d_ids[j], lens_out=d_lens[j])  # asynchronous enqueue
 
     def step_e2e(i):
-        eng.transcribe_tokens(h_sets[i & 1], ids_out=h_ids, lens_out=h_lens)  # H2D + compute + D2H, returns synced
+        j = i % n_eng
+        engs[j].transcribe_tokens(h_sets[i % n_sets], ids_out=h_ids[j], lens_out=h_lens[j])  # H2D + compute + D2H, returns synced
 
-    def timed(fn, steps):
+    from concurrent.futures import ThreadPoolExecutor
+    workers = [ThreadPoolExecutor(1) for _ in range(n_eng)]  # one host thread per engine (the C call releases the GIL)
+
+    def timed(fn, steps, threaded=False):
         torch.cuda.synchronize()
         if dist:
             dist.barrier()
         torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(stream)
-        for i in range(steps):
-            fn(i)
+        for st_ in streams[1:]:
+            st_.wait_event(a)
+        if threaded:
+            for f in [workers[i % n_eng].submit(fn, i) for i in range(steps)]:
+                f.result()
+        else:
+            for i in range(steps):
+                fn(i)
+        for st_ in streams[1:]:
+            stream.wait_stream(st_)
         b.record(stream)
         torch.cuda.synchronize()
         ms = a.elapsed_time(b)
@@ -233,29 +254,30 @@ def run_gpu(args):
             dist.barrier()
         return ms
 
-    for i in range(args.warmup):
+    for i in range(args.warmup * n_eng):   # W warm-up steps per engine
         step_dev(i)
-    l0 = eng.launch_count
+    l0 = sum(e.launch_count for e in engs)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     ms = timed(step_dev, args.steps)
-    launches = eng.launch_count - l0
+    launches = sum(e.launch_count for e in engs) - l0
     clocks = sampler.stop() if rank == 0 else None
-    for i in range(min(args.warmup, 2)):
+    for i in range(max(n_eng, min(args.warmup, 2))):
         step_e2e(i)
-    ms_e2e = timed(step_e2e, args.steps)
+    ms_e2e = timed(step_e2e, args.steps, threaded=n_eng > 1)
 
     # per-stage device times (CUDA events around every launch, same stream) for the roofline
     prof_steps = max(1, min(args.steps, 3))
+    torch.cuda.synchronize()
     eng.profile(True)
-    for i in range(prof_steps):
-        step_dev(i)
+    for i in range(prof_steps):   # engine 0 alone, steps back to back: per-kernel durations without co-running kernels
+        eng.transcribe_tokens(d_sets[i % n_sets], ids_out=d_ids[0], lens_out=d_lens[0])
     stages = eng.profile_read()
     eng.profile(False)
     # result sanity: every clip produced the prompt + generated tokens
     torch.cuda.synchronize()
-    lens_ok = bool(((d_lens >= 5) & (d_lens <= capi.MAX_TOKENS)).all().item())
+    lens_ok = all(bool(((dl >= 5) & (dl <= capi.MAX_TOKENS)).all().item()) for dl in d_lens)
 
     if rank == 0:
         pk = peaks()
@@ -319,8 +341,12 @@ def run_gpu(args):
                                    "log-mel + encoder + greedy decode (4 prompt + <=27 new tokens), 64 synthetic 30 s "
                                    "clips per GPU, seeded random-init weights",
                        "clips_per_gpu": B, "audio_seconds_per_step": audio_s, "parallelism": f"clip-sharded x{world}, "
-                       "no data-path collective", "l2": "no explicit flush: two rotating 123 MB PCM sets and >1 GB of "
-                       "activations per step exceed the 126 MB L2"},
+                       "no data-path collective",
+                       "pipeline": (f"{n_eng} engines per GPU on separate streams, batches alternate between them (batch i's "
+                                    "decoder overlaps batch i+1's mel + encoder); decoder 16 clips per cluster"
+                                    if n_eng > 1 else "1 engine, steps back to back"),
+                       "l2": "no explicit flush: three rotating 123 MB PCM sets and >1 GB of activations per step "
+                             "exceed the 126 MB L2"},
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": int(world * B * 480000 * 4),
@@ -355,6 +381,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--engines", type=int, default=2, help="engines per GPU that batches alternate between (1 = no pipelining)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

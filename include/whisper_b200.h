@@ -83,6 +83,13 @@ WT_API int wt_set_mel_filters(wt_engine* e, const float* filters, int n_mel, int
 /* Work is enqueued on `cuda_stream` (a cudaStream_t; NULL = the engine's own stream). Calls taking only
  * WT_DEVICE buffers return after enqueueing; calls touching a WT_HOST buffer synchronise before returning. */
 WT_API int wt_set_stream(wt_engine* e, void* cuda_stream);
+
+/* Clips per thread-block cluster of the persistent greedy decoder (1..16; 0 = automatic: spread the batch over every
+ * cluster that is co-resident on an otherwise idle GPU — lowest latency of a single call). A serving loop that keeps
+ * several engines busy on one GPU (batches alternating between engines on separate streams, so one batch's decoder
+ * overlaps the next batch's mel + encoder) sets 16: the decoder then occupies the fewest SMs per batch.
+ * New in this library (the reference decodes one clip per call: whisper.cpp:363-402). */
+WT_API int wt_set_decoder_group(wt_engine* e, int clips_per_cluster);
 WT_API int wt_synchronize(wt_engine* e);
 
 /* pcm [n_clips][n_samples] f32 -> mel_out [n_clips][80][n_samples/160] f32 (reference layout j*n_len+i).

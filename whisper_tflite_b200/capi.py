@@ -28,6 +28,7 @@ EXPORTED = [
     "wt_synchronize", "wt_log_mel", "wt_encode", "wt_decode_greedy", "wt_transcribe_tokens",
     "wt_get_step_logits", "wt_launch_count", "wt_last_error", "wt_version", "wt_debug_gemm_bf16",
     "wt_profile_enable", "wt_profile_read", "wt_stage_count", "wt_stage_name", "wt_debug_decoder_trace",
+    "wt_set_decoder_group",
 ]
 
 
@@ -124,6 +125,10 @@ class Engine:
     def set_stream(self, cuda_stream: int):
         _check(self.lib.wt_set_stream(self.h, ctypes.c_void_p(cuda_stream)))
 
+    def set_decoder_group(self, clips_per_cluster: int):
+        """Clips per decoder cluster (0 = automatic, 16 = fewest SMs per batch: for pipelined serving)."""
+        _check(self.lib.wt_set_decoder_group(self.h, int(clips_per_cluster)))
+
     def synchronize(self):
         _check(self.lib.wt_synchronize(self.h))
 
@@ -218,3 +223,46 @@ def debug_gemm_bf16(a, w, bias, c, flags: int = 0, stream: int = 0):
                                   ctypes.c_void_p(bias.data_ptr()) if bias is not None else None,
                                   ctypes.c_void_p(c.data_ptr()), M, N, K, flags | (1 if bias is not None else 0)))
     return c
+
+
+class EnginePool:
+    """Serving arrangement for one GPU: `n_engines` engines (replicated weights, one CUDA stream each) that take
+    batches in turn, so batch i's greedy decoder — latency-bound, a few thread-block clusters — runs underneath batch
+    i+1's mel frontend and encoder (tensor-bound, every SM the decoder leaves free). Each engine keeps the reference's
+    contract (calls on ONE engine are serialised by its caller: Whisper.java:109-113); the pool only decides which
+    engine a batch goes to. Host-buffer batches are driven by one thread per engine (the C call releases the GIL), so
+    the H2D copy of a batch also overlaps the other engine's compute."""
+
+    def __init__(self, weights_path: str, n_engines: int = 2, device: int = 0, max_batch: int = 64,
+                 precision: int = PRECISION_BF16, decoder_group: int = 16):
+        from concurrent.futures import ThreadPoolExecutor
+        self.engines = [Engine(weights_path, device=device, max_batch=max_batch, precision=precision)
+                        for _ in range(n_engines)]
+        for e in self.engines:
+            e.set_decoder_group(decoder_group if n_engines > 1 else 0)
+        self._workers = [ThreadPoolExecutor(1) for _ in self.engines]
+        self._next = 0
+
+    def submit(self, pcm, ids_out=None, lens_out=None):
+        """Queue one batch on the next engine; returns a future of (ids, lens)."""
+        i = self._next
+        self._next = (i + 1) % len(self.engines)
+        return self._workers[i].submit(self.engines[i].transcribe_tokens, pcm, ids_out=ids_out, lens_out=lens_out)
+
+    def transcribe_tokens_many(self, batches):
+        """Token ids of every batch, in order."""
+        return [f.result() for f in [self.submit(b) for b in batches]]
+
+    @property
+    def launch_count(self) -> int:
+        return sum(e.launch_count for e in self.engines)
+
+    def synchronize(self):
+        for e in self.engines:
+            e.synchronize()
+
+    def close(self):
+        for w in self._workers:
+            w.shutdown(wait=True)
+        for e in self.engines:
+            e.close()

@@ -123,10 +123,10 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred P1;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2, %3;\n\t"
       "selp.u32 %0, 1, 0, P1;\n\t}"
       : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(20000)   // suspend-time hint (ns): sleep in hardware, not in the issue slots
       : "memory");
   return ok != 0;
 }
@@ -322,6 +322,7 @@ struct DsRing {
 
 // One 8-column group per warp and round, accumulated over kph ring stages of upw units (2 MMAs each, two independent
 // accumulator chains). Returns with the warp's 16 x 8 tile in acc (rows g / g+8, columns 2t, 2t+1 of the group).
+template <bool kEarly>
 __device__ __forceinline__ void ds_mma_round(uint8_t* smem, const DsParams& p, DsRing& rg, const uint8_t* ring,
                                              const uint8_t* a_lane, int as, int upw, int kph, int nact,
                                              float (&acc)[4]) {
@@ -330,6 +331,36 @@ __device__ __forceinline__ void ds_mma_round(uint8_t* smem, const DsParams& p, D
   uint64_t* full = ds_full(smem);
   uint64_t* empty = ds_empty(smem);
   float a0[4] = {0.0f, 0.0f, 0.0f, 0.0f}, a1[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+  if constexpr (kEarly) {
+  for (int h = 0; h < kph; ++h) {
+    mbar_wait(full + rg.slot, rg.par);
+    const uint8_t* wp = ring + (size_t)rg.slot * kDsStageBytes + (size_t)(warp * upw) * kDsUnitBytes + lane * 16;
+    const uint8_t* ap = a_lane + (size_t)(h * upw) * 64;
+    // weights leave the ring in groups of <= 6 units (24 registers); the stage goes back to the producer as soon as the
+    // last group is in registers, before its MMAs — the slot is held for the loads only
+    for (int u0 = 0; u0 < upw; u0 += 6) {
+      uint4 w[6];
+#pragma unroll
+      for (int u = 0; u < 6; ++u)
+        if (active && u0 + u < upw) w[u] = *reinterpret_cast<const uint4*>(wp + (u0 + u) * kDsUnitBytes);
+      if (u0 + 6 >= upw) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty + rg.slot);
+        rg.advance(p.n_stages);
+      }
+      if (active) {
+#pragma unroll
+        for (int u = 0; u < 6; ++u)
+          if (u0 + u < upw) {
+            const uint4 lo = *reinterpret_cast<const uint4*>(ap + (u0 + u) * 64);
+            const uint4 hi = *reinterpret_cast<const uint4*>(ap + (u0 + u) * 64 + 8 * as);
+            mma_bf16_16816(a0, lo.x, hi.x, lo.y, hi.y, w[u].x, w[u].y);
+            mma_bf16_16816(a1, lo.z, hi.z, lo.w, hi.w, w[u].z, w[u].w);
+          }
+      }
+    }
+  }
+  } else {
   for (int h = 0; h < kph; ++h) {
     mbar_wait(full + rg.slot, rg.par);
     if (active) {
@@ -347,6 +378,7 @@ __device__ __forceinline__ void ds_mma_round(uint8_t* smem, const DsParams& p, D
     __syncwarp();
     if (lane == 0) mbar_arrive(empty + rg.slot);
     rg.advance(p.n_stages);
+  }
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j) acc[j] = a0[j] + a1[j];
@@ -391,7 +423,7 @@ __device__ __forceinline__ void ds_gemm(uint8_t* smem, const DsParams& p, DsRing
     {
       const int nact = (ng - rho * 8 < 8) ? ng - rho * 8 : 8;
       const int upw = nact == 8 ? upw_f : upw_l;
-      ds_mma_round(smem, p, rg, ring, a_lane, as, upw, nact == 8 ? kph_f : kph_l, nact, acc);
+      ds_mma_round<false>(smem, p, rg, ring, a_lane, as, upw, nact == 8 ? kph_f : kph_l, nact, acc);
     }
     if (tr) { const unsigned long long t_ = dec_globaltimer(); atomicAdd(p.trace + 12, t_ - tm); tm = t_; }
     if (!active) continue;
@@ -505,7 +537,7 @@ __device__ __noinline__ void ds_logits(uint8_t* smem, const DsParams& p, DsRing&
     float acc[4];
     {
       const int nact = (ng - rho * 8 < 8) ? ng - rho * 8 : 8;
-      ds_mma_round(smem, p, rg, ring, a_lane, as, nact == 8 ? upw_f : upw_l, nact == 8 ? kph_f : kph_l, nact, acc);
+      ds_mma_round<false>(smem, p, rg, ring, a_lane, as, nact == 8 ? upw_f : upw_l, nact == 8 ? kph_f : kph_l, nact, acc);
     }
     if (!active) continue;
     const float v00 = acc[0] + bz.x, v01 = acc[1] + bz.y, v10 = acc[2] + bz.x, v11 = acc[3] + bz.y;

@@ -272,6 +272,7 @@ struct wt_engine {
   // persistent decoder (bf16, d_model <= 768): one launch, one thread-block cluster per group of clips
   bool dec_persistent = false;
   int dec_cluster = 0, dec_group = 0, dec_groups_cap = 0, dec_active_clusters = 0;
+  int dec_group_user = 0;  // wt_set_decoder_group (0 = automatic)
   wt::DecLayerDev* d_dec_layers = nullptr;
   float *pd_x = nullptr, *pd_qs = nullptr, *pd_att = nullptr, *pd_qx = nullptr, *pd_xpart = nullptr;
   bf16* pd_hmid = nullptr;
@@ -905,11 +906,15 @@ int wt_engine::decode_persistent(int n_clips, int prompt_len, int max_total, int
   const int d = dims.d_model, H = dims.n_heads, S = dims.n_audio_ctx;
   // one wave: grow the group (up to kDecGroupMax clips) until every cluster of the launch is co-resident
   int gsz = dec_group;
-  if (!getenv("WT_DEC_GROUP")) {
+  if (dec_group_user > 0) {
+    gsz = dec_group_user;
+  } else if (!getenv("WT_DEC_GROUP")) {
     const int need = (n_clips + dec_active_clusters - 1) / dec_active_clusters;
     if (need > gsz) gsz = need < wt::kDecGroupMax ? need : wt::kDecGroupMax;
   }
   const int n_groups = (n_clips + gsz - 1) / gsz;
+  if (n_groups > dec_groups_cap)
+    return fail(WT_ERR_INVALID, "decoder: %d clip groups of %d exceed the %d the scratch buffers were sized for", n_groups, gsz, dec_groups_cap);
   WT_CUDA_OK(cudaMemsetAsync(pd_finished, 0, (size_t)dec_groups_cap * sizeof(int), stream));
   if (dec_stream) {
     wt::DsParams q{};
@@ -1408,6 +1413,13 @@ int wt_get_step_logits(wt_engine* e, int step, int n_clips, float* out, int out_
 }
 
 int64_t wt_launch_count(const wt_engine* e) { return e ? e->launches : 0; }
+int wt_set_decoder_group(wt_engine* e, int clips_per_cluster) {
+  if (!e) return fail(WT_ERR_INVALID, "null engine");
+  if (clips_per_cluster < 0 || clips_per_cluster > wt::kDecGroupMax)
+    return fail(WT_ERR_INVALID, "clips_per_cluster must be in [0, %d]", wt::kDecGroupMax);
+  e->dec_group_user = clips_per_cluster;
+  return WT_OK;
+}
 
 int wt_debug_decoder_trace(wt_engine* e, uint64_t* out32, int reset) {
   if (!e || !out32) return fail(WT_ERR_INVALID, "null argument");
