@@ -273,6 +273,7 @@ struct wt_engine {
   bool dec_persistent = false;
   int dec_cluster = 0, dec_group = 0, dec_groups_cap = 0, dec_active_clusters = 0;
   int dec_group_user = 0;  // wt_set_decoder_group (0 = automatic)
+  int* gemm_sched = nullptr;  // {next tile, CTAs done} of the GEMM kernel's dynamic tile scheduler (self-resetting)
   wt::DecLayerDev* d_dec_layers = nullptr;
   float *pd_x = nullptr, *pd_qs = nullptr, *pd_att = nullptr, *pd_qx = nullptr, *pd_xpart = nullptr;
   bf16* pd_hmid = nullptr;
@@ -398,6 +399,10 @@ static int launch_gemm_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMap
   p.n_tiles_n = (p.N + BN - 1) / BN;
   const int n_tiles = p.tiles_per_batch * p.n_batches * p.n_tiles_n;
   const int grid = n_tiles < e->num_sms ? n_tiles : e->num_sms;
+  if (!e->gemm_sched) {
+    if (e->alloc(&e->gemm_sched, 2, true) != WT_OK) return WT_ERR_CUDA;
+  }
+  p.sched = e->gemm_sched;
   e->pre_launch();
   wt::gemm_bf16_sm100_kernel<BN><<<grid, wt::kGemmThreads, S::kTotal, e->stream>>>(ma, mw, p);
   return e->check_launch("gemm_bf16_sm100_kernel");

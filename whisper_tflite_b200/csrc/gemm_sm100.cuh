@@ -63,6 +63,10 @@ struct GemmBf16Params {
   // coordinates (tap_c0[t] + kc*64, row0 + tap_row[t]) and the W tile at column t*tap_k + kc*64.
   int taps, kblocks_per_tap, tap_k;
   int tap_c0[3], tap_row[3];
+  // dynamic tile scheduler: sched[0] = next tile, sched[1] = CTAs done (the last one resets both for the next launch on
+  // the stream). A CTA takes tiles as fast as it can drain them, so a launch that shares the GPU with another stream's
+  // kernels (the other engine's decoder holds 64 SMs) needs no second wave of CTAs to cover the tile space.
+  int* sched;
 };
 
 // ---------------------------------------------------------------------------------------------------
@@ -201,7 +205,8 @@ struct GemmSmem {
   static constexpr int kScratchRowBytes = 128 + 16;  // 64 bf16 or 32 f32 per row + pad (keeps 16B phases conflict-free)
   static constexpr int kScratchBytes = kGemmEpiGroups * 4 * 32 * kScratchRowBytes;
   static constexpr int kBiasBytes = 2 * BN * 4;
-  static constexpr int kBarBytes = (2 * kStages + 4) * 8 + 16;
+  static constexpr int kTileQ = 4;      // tile-index queue producer -> MMA issuer + epilogue group (even: it & 1 keeps its group)
+  static constexpr int kBarBytes = (2 * kStages + 4 + 2 * kTileQ) * 8 + 16 + kTileQ * 4;
   static constexpr int kTotal = kStages * kStageBytes + kScratchBytes + kBiasBytes + kBarBytes + 1024;
   static constexpr int kTmemCols = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
 };
@@ -220,7 +225,10 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
   uint64_t* bar_empty = bar_full + S::kStages;
   uint64_t* bar_tfull = bar_empty + S::kStages;   // [2]
   uint64_t* bar_tempty = bar_tfull + 2;           // [2]
-  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_tempty + 2);
+  uint64_t* bar_qfull = bar_tempty + 2;           // [kTileQ] tile index published
+  uint64_t* bar_qempty = bar_qfull + S::kTileQ;   // [kTileQ] read by the MMA issuer and the four warps of one epilogue group
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_qempty + S::kTileQ);
+  volatile int* s_tileq = reinterpret_cast<volatile int*>(s_tmem + 4);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -239,6 +247,10 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
       mbar_init(bar_tfull + i, 1);
       mbar_init(bar_tempty + i, 4);  // one arrive per epilogue warp
     }
+    for (int i = 0; i < S::kTileQ; ++i) {
+      mbar_init(bar_qfull + i, 1);
+      mbar_init(bar_qempty + i, 5);  // MMA issuer + 4 epilogue warps
+    }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(s_tmem, S::kTmemCols);
@@ -252,7 +264,19 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      int n_end = 0;
+      for (int it = 0;; ++it) {
+        int tile = (n_end == 0) ? atomicAdd(p.sched, 1) : n_tiles;
+        if (tile >= n_tiles) tile = -1;
+        // publish: slot it % kTileQ (free once the MMA issuer and the epilogue group of tile it - kTileQ have read it)
+        const int qs = it % S::kTileQ;
+        mbar_wait(bar_qempty + qs, ((uint32_t)(it / S::kTileQ) & 1u) ^ 1u);
+        s_tileq[qs] = tile;
+        mbar_arrive(bar_qfull + qs);   // release: the store above is visible to whoever observes the phase
+        if (tile < 0) {
+          if (++n_end == 2) break;     // one end marker per epilogue group
+          continue;
+        }
         const int tn = tile % p.n_tiles_n, tm = tile / p.n_tiles_n;
         const int batch = tm / p.tiles_per_batch, row0 = (tm % p.tiles_per_batch) * kGemmBM;
         for (int kb = 0; kb < n_kblocks; ++kb) {
@@ -266,14 +290,26 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
           if (++stage == S::kStages) { stage = 0; phase ^= 1; }
         }
       }
+      // last CTA out re-arms the scheduler for the next launch on this stream
+      __threadfence();
+      if (atomicAdd(p.sched + 1, 1) == (int)gridDim.x - 1) {
+        p.sched[0] = 0;
+        p.sched[1] = 0;
+        __threadfence();
+      }
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
     constexpr uint32_t idesc = make_idesc_bf16(kGemmBM, BN);
     int stage = 0;
     uint32_t phase = 0;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+    for (int it = 0;; ++it) {
+      const int qs = it % S::kTileQ;
+      mbar_wait(bar_qfull + qs, (uint32_t)(it / S::kTileQ) & 1u);
+      const int tile = s_tileq[qs];
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_qempty + qs);
+      if (tile < 0) break;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(bar_tempty + acc, acc_phase ^ 1);  // epilogue has drained this accumulator
@@ -305,10 +341,14 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
     const int lane_q = warp & 3;        // TMEM lane quarter this warp may touch: lanes 32*(warp%4)..+31
     const int et = (threadIdx.x - 64) & 127;  // 0..127 within the group
     uint8_t* scr = s_scratch + ew * 32 * S::kScratchRowBytes;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-      const int acc = it & 1;
-      if (acc != eg) continue;
+    for (int it = eg;; it += 2) {   // this group's tiles: it & 1 == eg
+      const int acc = eg;
+      const int qs = it % S::kTileQ;
+      mbar_wait(bar_qfull + qs, (uint32_t)(it / S::kTileQ) & 1u);
+      const int tile = s_tileq[qs];
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_qempty + qs);
+      if (tile < 0) break;
       const uint32_t acc_phase = (it >> 1) & 1;
       const int tn = tile % p.n_tiles_n, tm = tile / p.n_tiles_n;
       const int batch = tm / p.tiles_per_batch, row0 = (tm % p.tiles_per_batch) * kGemmBM;
