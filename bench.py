@@ -328,6 +328,15 @@ def run_gpu(args):
             return None
 
         roofs = {k: roof(k) for k in ("mel_frames", "enc_gemm", "enc_attention", "dec_cross_attn", "dec_persistent")}
+        # traffic: DRAM bytes per launch from the committed `ncu --set full` capture of the same workload
+        # (profiles/traffic.json, written by tools/ncu_summary.py); single-kernel stages only
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["bytes_per_launch"]
+            for stage_name, kern in (("mel_frames", "mel_frames_kernel"), ("dec_persistent", "decoder_stream_kernel")):
+                if roofs.get(stage_name) and tr.get(kern):
+                    roofs[stage_name]["traffic"] = tr[kern][0]
+        except (OSError, KeyError, ValueError):
+            pass
         roofline = roofs.get(dom) or roofs["enc_gemm"] or {}
         roofline = dict(roofline)
         roofline["dominant_stage"] = dom

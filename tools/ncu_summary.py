@@ -25,6 +25,9 @@ WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio"]
 
 
+TRAFFIC = {}
+
+
 def launches(tag):
     path = os.path.join(OUT, f"{tag}_launches.csv")
     if not os.path.exists(path):
@@ -73,6 +76,16 @@ def full(tag):
                         f.write(f"| {w} | {r[i]} {units[i]} |\n")
                 f.write("\n")
         print("wrote", f"profiles/{name}.md")
+        # DRAM traffic per launch of each captured kernel (read + write), for bench.py's roofline.traffic
+        unit_b = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        for r in rows[2:]:
+            try:
+                ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+                byt = float(r[ir]) * unit_b[units[ir]] + float(r[iw]) * unit_b[units[iw]]
+            except (ValueError, KeyError):
+                continue
+            kname = r[hdr.index("Kernel Name")].split("(")[0].split("<")[0].replace("void ", "").replace("wt::", "").strip()
+            TRAFFIC.setdefault(kname, []).append(byt)
 
 
 if __name__ == "__main__":
@@ -80,3 +93,9 @@ if __name__ == "__main__":
     os.makedirs(PROF, exist_ok=True)
     launches(t)
     full(t)
+    if TRAFFIC:
+        import json
+        with open(os.path.join(PROF, "traffic.json"), "w") as f:
+            json.dump({"tag": t, "how": "ncu --set full: dram__bytes_read.sum + dram__bytes_write.sum per captured launch "
+                       "(tools/one_step.py: whisper-tiny, 64 clips)", "bytes_per_launch": TRAFFIC}, f, indent=1)
+        print("wrote profiles/traffic.json")
