@@ -370,6 +370,21 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
       const long long a_base = (p.flags & EPI_ADD) ? p.add_map.at(batch * p.rows_per_batch + row0) : 0ll;
 
       for (int c0 = 0; c0 < BN; c0 += 32) {
+        // the addend's 32 rows x 32 cols of this warp (coalesced 16-byte pieces) are requested first: their global
+        // latency runs underneath the TMEM load and the bias / GELU math
+        uint4 addv[4];
+        if (p.flags & EPI_ADD) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int piece = i * 32 + lane;          // 128 pieces of 8 bf16: 4 per row
+            const int rr = piece >> 2, pc = piece & 3;
+            const int rb = row0 + lane_q * 32 + rr;
+            const int col = n0 + c0 + pc * 8;
+            addv[i] = make_uint4(0u, 0u, 0u, 0u);
+            if (rb < p.rows_per_batch && col < p.N)
+              addv[i] = *reinterpret_cast<const uint4*>(p.addend + a_base + (long long)(rb - row0) * p.add_map.row_stride + col);
+          }
+        }
         uint32_t v[32];
         tmem_ld32(t_row + c0, v);
         tmem_ld_wait();
@@ -378,7 +393,10 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
         if (p.flags & EPI_BIAS) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] += bias_s[c0 + j];
+          for (int j = 0; j < 32; j += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(bias_s + c0 + j);
+            f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
+          }
         }
         if (p.flags & EPI_GELU) {
 #pragma unroll
@@ -389,14 +407,9 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
           __syncwarp();
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            const int piece = i * 32 + lane;          // 128 pieces of 8 bf16: 4 per row
+            const int piece = i * 32 + lane;
             const int rr = piece >> 2, pc = piece & 3;
-            const int rb = row0 + lane_q * 32 + rr;
-            const int col = n0 + c0 + pc * 8;
-            uint4 val = make_uint4(0u, 0u, 0u, 0u);
-            if (rb < p.rows_per_batch && col < p.N)
-              val = *reinterpret_cast<const uint4*>(p.addend + a_base + (long long)(rb - row0) * p.add_map.row_stride + col);
-            *reinterpret_cast<uint4*>(scr + rr * S::kScratchRowBytes + pc * 16) = val;
+            *reinterpret_cast<uint4*>(scr + rr * S::kScratchRowBytes + pc * 16) = addv[i];
           }
           __syncwarp();
 #pragma unroll
