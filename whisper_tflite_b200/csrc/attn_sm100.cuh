@@ -19,7 +19,7 @@
 
 namespace wt {
 
-constexpr int kAtThreads = 192;
+constexpr int kAtThreads = 64 + 256;   // TMA warp, MMA warp, 2 softmax warpgroups (keys 0-63 / 64-127 of every block)
 constexpr int kAtStages = 4;
 constexpr int kAtTile = 128 * 64 * 2;  // one 128 x 64 bf16 tile: 16 KB
 struct AttnSmem {
@@ -27,7 +27,8 @@ struct AttnSmem {
   static constexpr int kP = kQ + kAtTile;                 // 2 buffers x (2 sub-tiles of 128 x 64) = 64 KB
   static constexpr int kKV = kP + 4 * kAtTile;            // kAtStages x (K tile + V tile)
   static constexpr int kBars = kKV + kAtStages * 2 * kAtTile;
-  static constexpr int kTotal = kBars + 256 + 1024;
+  static constexpr int kXch = kBars + 256;                // row-max exchange between the two key halves: f32 [2 blocks][2][128]
+  static constexpr int kTotal = kXch + 2 * 2 * 128 * 4 + 1024;
 };
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -76,7 +77,7 @@ attention_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_s_full + i, 1);
-      mbar_init(bar_p_full + i, 4);
+      mbar_init(bar_p_full + i, 8);
       mbar_init(bar_o_full + i, 1);
     }
     fence_barrier_init();
@@ -146,52 +147,55 @@ attention_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
       if (j + 2 < nkb) issue_s(j + 2);
     }
   } else {
-    // ---- softmax + accumulate: thread <-> query row ----
-    const int quarter = warp & 3;
+    // ---- softmax + accumulate: two threads per query row, one per 64-key half of every block (sg); each folds half
+    //      of the O columns. The halves meet once per block to agree on the row maximum (shared memory + a 64-thread
+    //      named barrier per lane quarter) and once at the end for the row sum. ----
+    const int sg = (warp - 2) >> 2;       // key half of the block / dim half of O
+    const int quarter = warp & 3;         // TMEM lane quarter this warp may touch
     const int row = quarter * 32 + lane;
     const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
     const float c_scale = 0.125f * 1.4426950408889634f;  // 1/sqrt(64) * log2(e)
-    float o[64];
+    float* xch = reinterpret_cast<float*>(smem + AttnSmem::kXch);
+    float o[32];
 #pragma unroll
-    for (int i = 0; i < 64; ++i) o[i] = 0.0f;
+    for (int i = 0; i < 32; ++i) o[i] = 0.0f;
     float m_run = -INFINITY, l_run = 0.0f, alpha_prev = 0.0f;
-    uint8_t* p_row_base = smem + AttnSmem::kP + row * 128;
+    uint8_t* p_row_base = smem + AttnSmem::kP + sg * kAtTile + row * 128;
     const int sw = row & 7;
     for (int j = 0; j < nkb; ++j) {
       mbar_wait(bar_s_full + (j & 1), (uint32_t)((j >> 1) & 1));
       tc_fence_after();
-      const uint32_t t_s = tmem_s + lane_sel + (j & 1) * 128;
-      const int valid = S - j * 128;  // keys valid in this block (>= 128 except the last)
-      // the whole S row (128 f32) in registers with ONE wait: the four loads are in flight together
-      uint32_t sv[128];
-#pragma unroll
-      for (int c = 0; c < 4; ++c) tmem_ld32(t_s + c * 32, sv + c * 32);
+      const uint32_t t_s = tmem_s + lane_sel + (j & 1) * 128 + sg * 64;
+      const int valid = S - j * 128 - sg * 64;  // keys of this half that exist (>= 64 except in the clip's last block)
+      uint32_t sv[64];
+      tmem_ld32(t_s, sv);
+      tmem_ld32(t_s + 32, sv + 32);
       tmem_ld_wait();
-      // row max: four independent chains; only the clip's last key block carries a mask
-      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
-      if (valid >= 128) {
+      float mx0 = -INFINITY, mx1 = -INFINITY;
+      if (valid >= 64) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           mx0 = fmaxf(mx0, __uint_as_float(sv[i]));
           mx1 = fmaxf(mx1, __uint_as_float(sv[32 + i]));
-          mx2 = fmaxf(mx2, __uint_as_float(sv[64 + i]));
-          mx3 = fmaxf(mx3, __uint_as_float(sv[96 + i]));
         }
       } else {
 #pragma unroll
-        for (int i = 0; i < 128; ++i) {
+        for (int i = 0; i < 64; ++i) {
           if (i >= valid) sv[i] = 0xff800000u;  // -inf: exp2 -> 0, never the maximum
           mx0 = fmaxf(mx0, __uint_as_float(sv[i]));
         }
       }
-      const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+      float mx = fmaxf(mx0, mx1);
+      float* xr = xch + (j & 1) * 256;
+      xr[sg * 128 + row] = mx;
+      asm volatile("bar.sync %0, 64;" ::"r"(1 + quarter) : "memory");
+      mx = fmaxf(mx, xr[(sg ^ 1) * 128 + row]);
       const float m_new = fmaxf(m_run, mx * c_scale);
       const float alpha = ex2_approx(m_run - m_new);
-      // P = exp2(s*c - m), row sum (four chains), bf16 -> swizzled shared tile
       float l0 = 0.0f, l1 = 0.0f, l2 = 0.0f, l3 = 0.0f;
       uint8_t* p_row = p_row_base + (j & 1) * 2 * kAtTile;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < 2; ++c) {
         float pv[32];
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
@@ -201,35 +205,31 @@ attention_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
           pv[i + 3] = ex2_approx(fmaf(__uint_as_float(sv[c * 32 + i + 3]), c_scale, -m_new));
           l0 += pv[i]; l1 += pv[i + 1]; l2 += pv[i + 2]; l3 += pv[i + 3];
         }
-        // 32 keys = 4 chunks of 16 bytes; key block c*32 lies in sub-tile c/2, chunk index (c&1)*4 + q
-        uint8_t* sub = p_row + (c >> 1) * kAtTile;
+        // this half's 64 keys = 8 chunks of 16 bytes in sub-tile sg; keys c*32.. are chunks c*4 + q
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          const int chunk = ((c & 1) * 4 + q) ^ sw;
-          *reinterpret_cast<uint4*>(sub + chunk * 16) =
+          const int chunk = (c * 4 + q) ^ sw;
+          *reinterpret_cast<uint4*>(p_row + chunk * 16) =
               make_uint4(pack_bf16x2(pv[8 * q], pv[8 * q + 1]), pack_bf16x2(pv[8 * q + 2], pv[8 * q + 3]),
                          pack_bf16x2(pv[8 * q + 4], pv[8 * q + 5]), pack_bf16x2(pv[8 * q + 6], pv[8 * q + 7]));
         }
       }
-      const float l_blk = (l0 + l1) + (l2 + l3);
-      l_run = l_run * alpha + l_blk;
+      l_run = l_run * alpha + ((l0 + l1) + (l2 + l3));
       m_run = m_new;
       fence_proxy_async();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_p_full + (j & 1));
-      // fold the previous block's partial O into the register accumulator
+      // fold the previous block's partial O (this thread's 32 dims) into the register accumulator
       if (j >= 1) {
         const int jp = j - 1;
         mbar_wait(bar_o_full + (jp & 1), (uint32_t)((jp >> 1) & 1));
         tc_fence_after();
-        const uint32_t t_o = tmem_o + lane_sel + (jp & 1) * 64;
-        uint32_t v[64];
-        tmem_ld32(t_o, v);
-        tmem_ld32(t_o + 32, v + 32);
+        uint32_t v[32];
+        tmem_ld32(tmem_o + lane_sel + (jp & 1) * 64 + sg * 32, v);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 64; ++i) o[i] = fmaf(o[i], alpha_prev, __uint_as_float(v[i]));
+        for (int i = 0; i < 32; ++i) o[i] = fmaf(o[i], alpha_prev, __uint_as_float(v[i]));
       }
       alpha_prev = alpha;
     }
@@ -237,20 +237,23 @@ attention_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
       const int jp = nkb - 1;
       mbar_wait(bar_o_full + (jp & 1), (uint32_t)((jp >> 1) & 1));
       tc_fence_after();
-      const uint32_t t_o = tmem_o + lane_sel + (jp & 1) * 64;
-      uint32_t v[64];
-      tmem_ld32(t_o, v);
-      tmem_ld32(t_o + 32, v + 32);
+      uint32_t v[32];
+      tmem_ld32(tmem_o + lane_sel + (jp & 1) * 64 + sg * 32, v);
       tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < 64; ++i) o[i] = fmaf(o[i], alpha_prev, __uint_as_float(v[i]));
+      for (int i = 0; i < 32; ++i) o[i] = fmaf(o[i], alpha_prev, __uint_as_float(v[i]));
     }
+    // row sum = sum of the two halves' partial sums (both carry the same running maximum)
+    float* xl = xch + (nkb & 1) * 256;
+    xl[sg * 128 + row] = l_run;
+    asm volatile("bar.sync %0, 64;" ::"r"(1 + quarter) : "memory");
+    l_run += xl[(sg ^ 1) * 128 + row];
     const int q = q0 + row;
     if (q < S) {
       const float inv = 1.0f / l_run;
-      uint4* dst = reinterpret_cast<uint4*>(out + ((long long)b * S + q) * D + h * 64);
+      uint4* dst = reinterpret_cast<uint4*>(out + ((long long)b * S + q) * D + h * 64 + sg * 32);
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
+      for (int i = 0; i < 4; ++i)
         dst[i] = make_uint4(pack_bf16x2(o[8 * i] * inv, o[8 * i + 1] * inv), pack_bf16x2(o[8 * i + 2] * inv, o[8 * i + 3] * inv),
                             pack_bf16x2(o[8 * i + 4] * inv, o[8 * i + 5] * inv), pack_bf16x2(o[8 * i + 6] * inv, o[8 * i + 7] * inv));
     }
