@@ -69,3 +69,43 @@ def test_engine_pool_matches_single_engine():
         np.testing.assert_array_equal(lens, wl)
     assert pool.launch_count > 0
     pool.close()
+
+
+@pytest.mark.parametrize("size,n_clips", [("base", 3), ("small", 2)])
+def test_base_and_small_dims(size, n_clips, oracle_built, filters):
+    """BASELINE.json configs[3] / [4] architectures (random init): d = 512 (8 weight units per warp and stage, 8 heads)
+    and d = 768 (2-stage ring next to the 99 KB hidden tile, 12 + 12 layers). Encoder states against the oracle, the
+    streaming decoder against the per-kernel decoder on the same bf16 operands."""
+    import os
+
+    from oracle import model_ref
+    from tests.gpu_util import rel_to_max
+    from whisper_tflite_b200 import capi
+    path, dims, W = weight_file(size)
+    pcm = synth.synth_pcm(n_clips, seed=9)
+    os.environ["WT_DECODER"] = "legacy"
+    try:
+        old = capi.Engine(path, max_batch=n_clips, keep_logits=True)
+    finally:
+        del os.environ["WT_DECODER"]
+    new = capi.Engine(path, max_batch=n_clips, keep_logits=True)
+    new.log_mel(pcm)
+    states = new.encode(None, n_clips=n_clips)
+    mel0 = oracle_built.oracle_log_mel(pcm[0], filters, 8)
+    xa0 = model_ref.encoder_forward(W, dims, mel0)
+    assert rel_to_max(states[0], xa0) <= 3e-2
+    ids_new, lens_new = new.decode_greedy(n_clips)
+    ids_old, lens_old = old.transcribe_tokens(pcm)
+    assert np.all(lens_new >= 5)
+    for c in range(n_clips):
+        for s_ in range(27):
+            a, b = old.step_logits(s_, n_clips)[c], new.step_logits(s_, n_clips)[c]
+            err = np.abs(a - b).max()
+            assert err <= 2e-2 * np.abs(a).max(), (c, s_, err)
+            top2 = np.partition(a, -2)[-2:]
+            if top2[1] - top2[0] > 4 * err:
+                assert ids_old[c][4 + s_] == ids_new[c][4 + s_]
+            else:
+                break
+    old.close()
+    new.close()
