@@ -23,6 +23,7 @@
 
 #include "../../include/whisper_b200.h"
 #include "attn_sm100.cuh"
+#include "attn2_sm100.cuh"
 #include "decoder_sm100.cuh"
 #include "decoder_stream_sm100.cuh"
 #include "gemm_sm100.cuh"
@@ -1119,11 +1120,18 @@ int wt_engine::encode(const float* mel, int n_clips, int mel_mem, float* states_
       static bool attn_attr[64] = {};
       if (!attn_attr[device & 63]) {
         WT_CUDA_OK(cudaFuncSetAttribute(wt::attention_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::AttnSmem::kTotal));
+        WT_CUDA_OK(cudaFuncSetAttribute(wt::attention2_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::Attn2Smem::kTotal));
         attn_attr[device & 63] = true;
       }
+      static const bool one_cta = [] { const char* v = getenv("WT_ATTN"); return v && strcmp(v, "1cta") == 0; }();
       pre_launch();
-      wt::attention_sm100_kernel<<<dim3((S + 127) / 128, H, n_clips), wt::kAtThreads, wt::AttnSmem::kTotal, stream>>>(mq, (bf16*)att, S, H);
-      WT_TRY(check_launch("attention_sm100_kernel"));
+      if (one_cta) {
+        wt::attention_sm100_kernel<<<dim3((S + 127) / 128, H, n_clips), wt::kAtThreads, wt::AttnSmem::kTotal, stream>>>(mq, (bf16*)att, S, H);
+        WT_TRY(check_launch("attention_sm100_kernel"));
+      } else {  // two CTAs per SM (attn2_sm100.cuh)
+        wt::attention2_sm100_kernel<<<dim3((S + 127) / 128, H, n_clips), wt::kAt2Threads, wt::Attn2Smem::kTotal, stream>>>(mq, (bf16*)att, S, H);
+        WT_TRY(check_launch("attention2_sm100_kernel"));
+      }
     }
     WT_TRY(linear(att, M2, L.out, x, 0, x));
     WT_TRY(layernorm(x, L.ln2, xn, M2));
