@@ -711,8 +711,9 @@ __device__ __noinline__ unsigned dec_cross_attn(uint8_t* smem, const DecParams& 
       for (int u = 0; u < kU; ++u) {
         const int kl = u * (kDecWarps * 4) + warp * 4 + grp;
         ok[u] = kl < n_keys;
-        kq[u] = *reinterpret_cast<const uint4*>(st + (size_t)kl * 128 + sub * 16);
-        vq[u] = *reinterpret_cast<const uint4*>(st + (size_t)(kXaChunk + kl) * 128 + sub * 16);
+        const int sw = (sub ^ (kl & 7)) * 16;   // the stream's 16-byte segments are swizzled by key & 7 (gemm_sm100.cuh)
+        kq[u] = *reinterpret_cast<const uint4*>(st + (size_t)kl * 128 + sw);
+        vq[u] = *reinterpret_cast<const uint4*>(st + (size_t)(kXaChunk + kl) * 128 + sw);
         if (!ok[u]) {  // rows past the clip's last key are padding (never written): keep them out of the math
           kq[u] = make_uint4(0u, 0u, 0u, 0u);
           vq[u] = make_uint4(0u, 0u, 0u, 0u);

@@ -130,6 +130,11 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+#ifdef DS_PROBE
+constexpr bool kDsProbe = true;   // -DDS_PROBE: WT_DEC_DEBUG=4 / 8 skip the cross-attention / projection math (stream-rate probes)
+#else
+constexpr bool kDsProbe = false;
+#endif
 __device__ __forceinline__ void ds_cons_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kDsConsThreads) : "memory"); }
 __device__ __forceinline__ uint64_t l2_evict_last_policy() {
   uint64_t p;
@@ -363,7 +368,7 @@ __device__ __forceinline__ void ds_mma_round(uint8_t* smem, const DsParams& p, D
   } else {
   for (int h = 0; h < kph; ++h) {
     mbar_wait(full + rg.slot, rg.par);
-    if (active) {
+    if (active && !(kDsProbe && (p.debug & 8))) {   // WT_DEC_DEBUG=8 (timing probe build): consume the weight stream without the MMAs
       const uint8_t* wp = ring + (size_t)rg.slot * kDsStageBytes + (size_t)(warp * upw) * kDsUnitBytes + lane * 16;
       const uint8_t* ap = a_lane + (size_t)(h * upw) * 64;
 #pragma unroll 2
@@ -656,12 +661,125 @@ __device__ __noinline__ void ds_self_attn(uint8_t* smem, const DsParams& p, cons
 // ---- cross-attention: this CTA owns whole (clip, head) pairs; their K/V chunks arrive through the ring in order,
 //      their queries were pushed into s_q by the query projection's epilogue. 8 lanes share a key (8 dims each), 4 keys
 //      per warp and load. The finished 64-wide output goes, as bf16, into every CTA's operand tile. ----
+// four 8 x 8 bf16 matrices from shared memory: lanes 8i .. 8i+7 give the row addresses of matrix i
+__device__ __forceinline__ void ds_ldsm4(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr) : "memory");
+}
+__device__ __forceinline__ void ds_ldsm4_t(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr) : "memory");
+}
+// m16n8k16 with only row 0 of A alive (one query per (clip, head) pair): rows 8..15 of A are zero and their
+// accumulators are dead, so the instruction carries two live accumulator registers instead of four
+__device__ __forceinline__ void ds_mma_row0(float& c0, float& c1, uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
+  float d2, d3;
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%5}, {%7,%8}, {%0,%1,%9,%9};"
+      : "+f"(c0), "+f"(c1), "=f"(d2), "=f"(d3)
+      : "r"(a0), "r"(0u), "r"(a2), "r"(b0), "r"(b1), "f"(0.0f));
+}
+
+// One softmax step of a warp over its 16-key slabs of NCH consecutive chunks (ring stages) of a pair: with NCH = 2 the
+// two score chains, one max reduction and one rescale cover 32 keys, which halves the dependent latency per chunk —
+// the phase is bound by that chain, not by issue slots or the stream (WT_DEC_DEBUG=4 measures the stream alone).
+// (NCH = 2 measured slower on B200: two ring stages held at once and register spills around the call sites.)
+constexpr int kDsXaChunksPerStep = 1;
+template <int NCH>
+__device__ __forceinline__ void ds_xa_step(const DsParams& p, DsRing& rg, uint32_t ring, uint64_t* full, uint64_t* empty,
+                                           uint32_t k_off, uint32_t v_off, const uint32_t (&qa)[4][2], int n_keys_last,
+                                           float& m, float& lsum, float (&o)[8][2]) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  uint32_t vf[NCH][4][4];
+  float sc[NCH][2][2];
+#pragma unroll
+  for (int n = 0; n < NCH; ++n) {
+    mbar_wait(full + rg.slot, rg.par);
+    const uint32_t stg = ring + (uint32_t)rg.slot * kDsStageBytes;
+    if (!kDsProbe || !(p.debug & 4)) {  // WT_DEC_DEBUG=4 (timing probe build): consume the stream without the math
+      // K: load h of key tile j = matrices (keys 8j..8j+7) x segments 4h..4h+3 -> b0/b1 of k-steps 2h, 2h+1
+      uint32_t kf[2][2][4];
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) ds_ldsm4(stg + ((k_off + j * 1024u) ^ (uint32_t)(h * 64)), kf[j][h]);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        sc[n][j][0] = sc[n][j][1] = 0.0f;
+#pragma unroll
+        for (int s = 0; s < 4; ++s)
+          ds_mma_row0(sc[n][j][0], sc[n][j][1], qa[s][0], qa[s][1], kf[j][s >> 1][(s & 1) * 2], kf[j][s >> 1][(s & 1) * 2 + 1]);
+      }
+      // V (transposed on load): load q = matrices (keys lo | hi) x segments 2q, 2q+1 -> b0/b1 of dim tiles 2q, 2q+1.
+      // After the score MMAs: the K fragments are dead by then (register pressure), the softmax hides the latency.
+#pragma unroll
+      for (int q = 0; q < 4; ++q) ds_ldsm4_t(stg + (v_off ^ (uint32_t)(q * 32)), vf[n][q]);
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty + rg.slot);  // values are in registers: the producer may refill the stage
+    rg.advance(p.n_stages);
+  }
+  if (kDsProbe && (p.debug & 4)) return;
+  const int key0 = warp * 16 + 2 * t;   // sc[.][j][e] belongs to key key0 + 8j + e of its chunk
+  if (n_keys_last < kXaChunk) {         // only the last chunk of a pair can be short
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e)
+        if (key0 + 8 * j + e >= n_keys_last) sc[NCH - 1][j][e] = -1.0e30f;
+  }
+  float mx = fmaxf(fmaxf(sc[0][0][0], sc[0][0][1]), fmaxf(sc[0][1][0], sc[0][1][1]));
+  if (NCH == 2) mx = fmaxf(mx, fmaxf(fmaxf(sc[NCH - 1][0][0], sc[NCH - 1][0][1]), fmaxf(sc[NCH - 1][1][0], sc[NCH - 1][1][1])));
+  // lanes 0..3 hold the query's scores (the other rows of the fragment are zero rows): their quad maximum is the row's
+  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+  mx = __shfl_sync(0xffffffffu, mx, 0);
+  if (mx > m) {  // warp-uniform; rare after the first chunks
+    const float scale = dec_ex2(m - mx);
+    lsum *= scale;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      o[i][0] *= scale;
+      o[i][1] *= scale;
+    }
+    m = mx;
+  }
+#pragma unroll
+  for (int n = 0; n < NCH; ++n) {
+    float pw[2][2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) pw[j][e] = dec_ex2(sc[n][j][e] - m);
+    if (n == NCH - 1 && n_keys_last < kXaChunk) {  // a slab that is all padding has m == its masked score: force 0
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+          if (key0 + 8 * j + e >= n_keys_last) pw[j][e] = 0.0f;
+    }
+    lsum += (pw[0][0] + pw[0][1]) + (pw[1][0] + pw[1][1]);
+    const uint32_t pa0 = g == 0 ? dec_pack2(pw[0][0], pw[0][1]) : 0u;
+    const uint32_t pa2 = g == 0 ? dec_pack2(pw[1][0], pw[1][1]) : 0u;
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt)
+      ds_mma_row0(o[nt][0], o[nt][1], pa0, pa2, vf[n][nt >> 1][(nt & 1) * 2], vf[n][nt >> 1][(nt & 1) * 2 + 1]);
+  }
+}
+
+// Cross-attention over the (clip, head) pairs this CTA owns. A ring stage = one chunk of 128 keys (K rows then V rows,
+// 128 B each, 16-byte segments XOR-swizzled by key & 7 in the stream itself — gemm_sm100.cuh's K/V scatter — so that
+// ldmatrix reads them without bank conflicts). Warp w takes keys 16w .. 16w+15 of every chunk: scores = 8 mma (2 key
+// tiles x 4 k-steps over the 64 dims, A row 0 = the bf16 query), online softmax on the accumulator fragment (lanes
+// 0..3 hold the 16 scores), P goes straight back in as the A fragment of 8 more mma against V (ldmatrix.trans). The
+// 8 warps' partial (max, sum, O) are merged through shared memory once per pair.
 __device__ __noinline__ void ds_cross_attn(uint8_t* smem, const DsParams& p, DsRing& rg) {
+  static_assert(kXaChunk == kDsConsWarps * 16, "one 16-key slab per consumer warp and chunk");
   float* s_misc = reinterpret_cast<float*>(smem + DsSmem::kMisc);
   const float* s_q = reinterpret_cast<const float*>(smem + DsSmem::kXq);
-  const uint8_t* ring = smem + DsSmem::ring(p.d);
+  const uint32_t ring = smem_u32(smem + DsSmem::ring(p.d));
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int grp = lane >> 3, sub = lane & 7;
+  const int g = lane >> 2, t = lane & 3, r8 = lane & 7, mi = lane >> 3;
   const int d = p.d, H = p.H, S = p.S;
   const DsStream* st = ds_stream(smem);
   const int cpp = st->cpp;
@@ -672,91 +790,33 @@ __device__ __noinline__ void ds_cross_attn(uint8_t* smem, const DsParams& p, DsR
   float* sm_acc = s_misc + 16;      // [8][64]
   const uint32_t sa = smem_u32(smem + DsSmem::a_off(d));
   const int as = DsSmem::a_stride(d);
+  // this lane's ldmatrix row addresses inside a stage (see the fragment maps above the loads)
+  const uint32_t k_off = (uint32_t)(warp * 16 + r8) * 128u + (uint32_t)((mi ^ r8) << 4);
+  const uint32_t v_off = (uint32_t)(kXaChunk + warp * 16 + 8 * (mi & 1) + r8) * 128u + (uint32_t)(((mi >> 1) ^ r8) << 4);
   for (int si = 0; si < st->npairs; ++si) {
     const int pr = st->pair0 + si;
-    float qv[8];
-    {
-      const float4 q0 = *reinterpret_cast<const float4*>(s_q + si * 64 + sub * 8);
-      const float4 q1 = *reinterpret_cast<const float4*>(s_q + si * 64 + sub * 8 + 4);
-      qv[0] = q0.x; qv[1] = q0.y; qv[2] = q0.z; qv[3] = q0.w;
-      qv[4] = q1.x; qv[5] = q1.y; qv[6] = q1.z; qv[7] = q1.w;
+    uint32_t qa[4][2];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      const float2 x = *reinterpret_cast<const float2*>(s_q + si * 64 + 16 * s + 2 * t);
+      const float2 y = *reinterpret_cast<const float2*>(s_q + si * 64 + 16 * s + 8 + 2 * t);
+      qa[s][0] = g == 0 ? dec_pack2(x.x, x.y) : 0u;
+      qa[s][1] = g == 0 ? dec_pack2(y.x, y.y) : 0u;
     }
-    float m = -1.0e30f, lsum = 0.0f, acc[8];
+    float m = -1.0e30f, lsum = 0.0f, o[8][2];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) acc[i] = 0.0f;
-    for (int c = 0; c < cpp; ++c) {
-      const int n_keys = (S - c * kXaChunk < kXaChunk) ? S - c * kXaChunk : kXaChunk;
-      mbar_wait(full + rg.slot, rg.par);
-      const uint8_t* stg = ring + (size_t)rg.slot * kDsStageBytes;
-      constexpr int kU = kXaChunk / (kDsConsWarps * 4);
-      uint4 kq[kU], vq[kU];
-      bool ok[kU];
-#pragma unroll
-      for (int u = 0; u < kU; ++u) {
-        const int kl = u * (kDsConsWarps * 4) + warp * 4 + grp;
-        ok[u] = kl < n_keys;
-        kq[u] = *reinterpret_cast<const uint4*>(stg + (size_t)kl * 128 + sub * 16);
-        vq[u] = *reinterpret_cast<const uint4*>(stg + (size_t)(kXaChunk + kl) * 128 + sub * 16);
-        if (!ok[u]) {  // rows past the clip's last key are padding (never written): keep them out of the math
-          kq[u] = make_uint4(0u, 0u, 0u, 0u);
-          vq[u] = make_uint4(0u, 0u, 0u, 0u);
-        }
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(empty + rg.slot);  // values are in registers: the producer may refill the stage
-      rg.advance(p.n_stages);
-      float sc[kU];
-      float mx = m;
-#pragma unroll
-      for (int u = 0; u < kU; ++u) {
-        float s = 0.0f;
-        float kf[8];
-        bf16x8_to_f32(kq[u], kf);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) s = fmaf(qv[i], kf[i], s);
-        s += __shfl_xor_sync(0xffffffffu, s, 1);
-        s += __shfl_xor_sync(0xffffffffu, s, 2);
-        s += __shfl_xor_sync(0xffffffffu, s, 4);
-        sc[u] = s;
-        if (ok[u]) mx = fmaxf(mx, s);
-      }
-      const float scale = dec_ex2(m - mx);
-      lsum *= scale;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) acc[i] *= scale;
-      m = mx;
-#pragma unroll
-      for (int u = 0; u < kU; ++u) {
-        if (ok[u]) {
-          const float pw = dec_ex2(sc[u] - m);
-          lsum += pw;
-          float vf[8];
-          bf16x8_to_f32(vq[u], vf);
-#pragma unroll
-          for (int i = 0; i < 8; ++i) acc[i] = fmaf(pw, vf[i], acc[i]);
-        }
-      }
-    }
-    // merge the 4 key lanes of the warp (lanes with equal `sub` hold the same 8 dims)
-#pragma unroll
-    for (int o = 8; o <= 16; o <<= 1) {
-      const float m2 = __shfl_xor_sync(0xffffffffu, m, o);
-      const float l2 = __shfl_xor_sync(0xffffffffu, lsum, o);
-      const float mn = fmaxf(m, m2);
-      const float s1 = dec_ex2(m - mn), s2 = dec_ex2(m2 - mn);
-      lsum = lsum * s1 + l2 * s2;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float a2 = __shfl_xor_sync(0xffffffffu, acc[i], o);
-        acc[i] = acc[i] * s1 + a2 * s2;
-      }
-      m = mn;
-    }
+    for (int i = 0; i < 8; ++i) o[i][0] = o[i][1] = 0.0f;
+    const int n_last = S - (cpp - 1) * kXaChunk;   // keys in the pair's last chunk
+    for (int c = 0; c < cpp; ++c)
+      ds_xa_step<kDsXaChunksPerStep>(p, rg, ring, full, empty, k_off, v_off, qa, c + 1 == cpp ? n_last : kXaChunk, m, lsum, o);
+    lsum += __shfl_xor_sync(0xffffffffu, lsum, 1);
+    lsum += __shfl_xor_sync(0xffffffffu, lsum, 2);
     ds_cons_bar();  // s_misc free (previous pair's merge done)
-    if (grp == 0) {
+    if (g == 0) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) sm_acc[warp * 64 + sub * 8 + i] = acc[i];
-      if (sub == 0) {
+      for (int nt = 0; nt < 8; ++nt)
+        *reinterpret_cast<float2*>(sm_acc + warp * 64 + 8 * nt + 2 * t) = make_float2(o[nt][0], o[nt][1]);
+      if (t == 0) {
         sm_m[warp] = m;
         sm_l[warp] = lsum;
       }

@@ -483,8 +483,10 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
                 __nv_bfloat16* dst;
                 if (p.kv_chunk > 0) {
                   const int ch = sq / p.kv_chunk, kin = sq - ch * p.kv_chunk;
+                  // 16-byte segments of a key's 128-byte row are XOR-swizzled by key & 7: the decoder reads the chunk
+                  // with ldmatrix straight out of the bulk-copied stage (decoder_stream_sm100.cuh: ds_cross_attn)
                   dst = p.kv_k + ((((size_t)(clip * p.kv_H + (cc >> 6)) * p.kv_cpp + ch) * 2 + which) * p.kv_chunk + kin) * 64 +
-                        (cc & 63);
+                        (((((cc & 63) >> 3) ^ (kin & 7)) << 3));
                 } else {
                   dst = (which ? p.kv_v : p.kv_k) + (((size_t)(clip * p.kv_H + (cc >> 6)) * p.kv_S + sq) * 64 + (cc & 63));
                 }
