@@ -319,7 +319,8 @@ struct DsRing {
   unsigned cons;  // stages consumed so far
   int slot;
   unsigned par;
-  __device__ __forceinline__ void advance(int n_stages) {
+  int n_stages;   // ring depth (a register copy: DsParams lives in shared memory and every barrier asm clobbers memory)
+  __device__ __forceinline__ void advance() {
     ++cons;
     if (++slot == n_stages) { slot = 0; par ^= 1u; }
   }
@@ -351,7 +352,7 @@ __device__ __forceinline__ void ds_mma_round(uint8_t* smem, const DsParams& p, D
       if (u0 + 6 >= upw) {
         __syncwarp();
         if (lane == 0) mbar_arrive(empty + rg.slot);
-        rg.advance(p.n_stages);
+        rg.advance();
       }
       if (active) {
 #pragma unroll
@@ -382,7 +383,7 @@ __device__ __forceinline__ void ds_mma_round(uint8_t* smem, const DsParams& p, D
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(empty + rg.slot);
-    rg.advance(p.n_stages);
+    rg.advance();
   }
   }
 #pragma unroll
@@ -516,7 +517,7 @@ __device__ __forceinline__ void ds_embed(uint8_t* smem, const DsParams& p, int p
 
 // ---- final LayerNorm -> tied logits with a fused (max, last index) per row (whisper.cpp:346-361's tie rule); this
 //      CTA's winners go to every peer's s_amax[rank][row] ----
-__device__ __noinline__ void ds_logits(uint8_t* smem, const DsParams& p, DsRing& rg, int pos) {
+__device__ __noinline__ DsRing ds_logits(uint8_t* smem, const DsParams& p, DsRing rg, int pos) {
   const DsStream* st = ds_stream(smem);
   const int d = p.d, B = p.n_clips, V = p.V, as = DsSmem::a_stride(d);
   const uint8_t* sA = smem + DsSmem::a_off(d);
@@ -577,6 +578,7 @@ __device__ __noinline__ void ds_logits(uint8_t* smem, const DsParams& p, DsRing&
   }
   ds_cons_bar();
   if (tid < B) ds_push_all(smem_u32(smem + DsSmem::kAmax) + (p.rank * kDsRows + tid) * 8, s_best[tid], p.G);
+  return rg;
 }
 
 // ---- every CTA reduces the cluster's partial winners itself (identical results everywhere): token of the step, EOT
@@ -717,7 +719,7 @@ __device__ __forceinline__ void ds_xa_step(const DsParams& p, DsRing& rg, uint32
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(empty + rg.slot);  // values are in registers: the producer may refill the stage
-    rg.advance(p.n_stages);
+    rg.advance();
   }
   if (kDsProbe && (p.debug & 4)) return;
   const int key0 = warp * 16 + 2 * t;   // sc[.][j][e] belongs to key key0 + 8j + e of its chunk
@@ -773,7 +775,7 @@ __device__ __forceinline__ void ds_xa_step(const DsParams& p, DsRing& rg, uint32
 // tiles x 4 k-steps over the 64 dims, A row 0 = the bf16 query), online softmax on the accumulator fragment (lanes
 // 0..3 hold the 16 scores), P goes straight back in as the A fragment of 8 more mma against V (ldmatrix.trans). The
 // 8 warps' partial (max, sum, O) are merged through shared memory once per pair.
-__device__ __noinline__ void ds_cross_attn(uint8_t* smem, const DsParams& p, DsRing& rg) {
+__device__ __noinline__ DsRing ds_cross_attn(uint8_t* smem, const DsParams& p, DsRing rg) {
   static_assert(kXaChunk == kDsConsWarps * 16, "one 16-key slab per consumer warp and chunk");
   float* s_misc = reinterpret_cast<float*>(smem + DsSmem::kMisc);
   const float* s_q = reinterpret_cast<const float*>(smem + DsSmem::kXq);
@@ -840,6 +842,7 @@ __device__ __noinline__ void ds_cross_attn(uint8_t* smem, const DsParams& p, DsR
       ds_push_all(sa + b * as + (h * 64 + 2 * tid) * 2, dec_pack2(o0 * inv, o1 * inv), p.G);
     }
   }
+  return rg;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -989,7 +992,7 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
     unsigned long long tlast = (p.trace != nullptr && tid == 0) ? dec_globaltimer() : 0ull;
     unsigned cphase = 0;
     DsRing rg;
-    rg.cons = 0; rg.slot = 0; rg.par = 0;
+    rg.cons = 0; rg.slot = 0; rg.par = 0; rg.n_stages = p.n_stages;
     float2 xr[2][2];
 #pragma unroll
     for (int i = 0; i < 2; ++i) xr[i][0] = xr[i][1] = make_float2(0.0f, 0.0f);
@@ -1007,7 +1010,7 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
           if (ph == 2) {
             ds_self_attn(ds_smem, p, p.layers[l], pos);
           } else if (ph == 5) {
-            ds_cross_attn(ds_smem, p, rg);
+            rg = ds_cross_attn(ds_smem, p, rg);
           } else {
             const int kind = ph == 1 ? DS_QKV : ph == 3 ? DS_OUT : ph == 4 ? DS_XQ : ph == 6 ? DS_XOUT : ph == 7 ? DS_FC1 : DS_FC2;
             ds_gemm(ds_smem, p, rg, kind, l, pos, xr);
@@ -1016,7 +1019,7 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
         }
       }
       if (pos >= p.prompt_len - 1) {
-        ds_logits(ds_smem, p, rg, pos);
+        rg = ds_logits(ds_smem, p, rg, pos);
         ds_cluster_sync(ds_smem, p, cphase, 9, tlast);
         if (ds_finalize(ds_smem, p, pos) >= B) break;  // every clip has produced EOT (whisper.cpp:397-399, per clip)
       }
