@@ -15,6 +15,118 @@
 
 namespace wt {
 
+// Softmax passes of one 128-key block for one query row, S read from TMEM in 32-column pieces. Both passes keep the NEXT
+// piece's tcgen05.ld in flight while the current one is processed (tcgen05.wait::ld covers every outstanding load, so
+// the order is wait -> issue next -> compute); the mask of a clip's last key block is a template flag behind a real
+// branch — as a run-time condition inside the unrolled body ptxas if-converts it into three predicated-off
+// instructions per element, which cost issue slots in every full block.
+template <bool kMasked>
+__device__ __forceinline__ float at2_piece_max(const uint32_t (&v)[32], int c, int valid) {
+  if (!kMasked) {
+    float m0 = -INFINITY, m1 = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < 32; i += 2) {
+      m0 = fmaxf(m0, __uint_as_float(v[i]));
+      m1 = fmaxf(m1, __uint_as_float(v[i + 1]));
+    }
+    return fmaxf(m0, m1);
+  } else {
+    float mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (c * 32 + i < valid) ? __uint_as_float(v[i]) : -INFINITY);
+    return mx;
+  }
+}
+// pass 1: row maximum of the block (raw scores)
+template <bool kMasked, bool kPrefetch>
+__device__ __forceinline__ float at2_pass1(uint32_t t_s, int valid) {
+  float mx;
+  if (kPrefetch) {
+    uint32_t va[32], vb[32];
+    tmem_ld32(t_s, va);
+    tmem_ld_wait();
+    tmem_ld32(t_s + 32, vb);
+    mx = at2_piece_max<kMasked>(va, 0, valid);
+    tmem_ld_wait();
+    tmem_ld32(t_s + 64, va);
+    mx = fmaxf(mx, at2_piece_max<kMasked>(vb, 1, valid));
+    tmem_ld_wait();
+    tmem_ld32(t_s + 96, vb);
+    mx = fmaxf(mx, at2_piece_max<kMasked>(va, 2, valid));
+    tmem_ld_wait();
+    mx = fmaxf(mx, at2_piece_max<kMasked>(vb, 3, valid));
+  } else {
+    mx = -INFINITY;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t v[32];
+      tmem_ld32(t_s + c * 32, v);
+      tmem_ld_wait();
+      mx = fmaxf(mx, at2_piece_max<kMasked>(v, c, valid));
+    }
+  }
+  return mx;
+}
+// one piece of pass 2: P = exp2(s * c - m) -> bf16 into the 128B-swizzled P tile (32-bit shared addresses); returns the
+// piece's row sum. 32 keys = 4 chunks of 16 bytes; key piece c lies in sub-tile c/2, chunk index (c&1)*4 + q.
+template <bool kMasked>
+__device__ __forceinline__ float at2_piece_exp(uint32_t (&v)[32], int c, uint32_t p_row_s, int sw, float c_scale, float m_new,
+                                               int valid) {
+  float la = 0.0f, lb = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 32; i += 2) {
+    float p0 = ex2_approx(fmaf(__uint_as_float(v[i]), c_scale, -m_new));
+    float p1 = ex2_approx(fmaf(__uint_as_float(v[i + 1]), c_scale, -m_new));
+    if (kMasked) {
+      if (c * 32 + i >= valid) p0 = 0.0f;
+      if (c * 32 + i + 1 >= valid) p1 = 0.0f;
+    }
+    la += p0;
+    lb += p1;
+    v[i >> 1] = pack_bf16x2(p0, p1);   // in place: word i/2 is dead by now (i/2 <= i)
+  }
+  const uint32_t sub = p_row_s + (uint32_t)((c >> 1) * kAtTile);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int chunk = ((c & 1) * 4 + q) ^ sw;
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sub + chunk * 16), "r"(v[4 * q]), "r"(v[4 * q + 1]),
+                 "r"(v[4 * q + 2]), "r"(v[4 * q + 3])
+                 : "memory");
+  }
+  return la + lb;
+}
+template <bool kMasked, bool kPrefetch>
+__device__ __forceinline__ float at2_pass2(uint32_t t_s, uint32_t p_row_s, int sw, float c_scale, float m_new, int valid) {
+  float l_blk = 0.0f;
+  if (kPrefetch) {
+    uint32_t va[32], vb[32];
+    tmem_ld32(t_s, va);
+    tmem_ld_wait();
+    tmem_ld32(t_s + 32, vb);
+    l_blk = at2_piece_exp<kMasked>(va, 0, p_row_s, sw, c_scale, m_new, valid);
+    tmem_ld_wait();
+    tmem_ld32(t_s + 64, va);
+    l_blk += at2_piece_exp<kMasked>(vb, 1, p_row_s, sw, c_scale, m_new, valid);
+    tmem_ld_wait();
+    tmem_ld32(t_s + 96, vb);
+    l_blk += at2_piece_exp<kMasked>(va, 2, p_row_s, sw, c_scale, m_new, valid);
+    tmem_ld_wait();
+    l_blk += at2_piece_exp<kMasked>(vb, 3, p_row_s, sw, c_scale, m_new, valid);
+  } else {
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t v[32];
+      tmem_ld32(t_s + c * 32, v);
+      tmem_ld_wait();
+      l_blk += at2_piece_exp<kMasked>(v, c, p_row_s, sw, c_scale, m_new, valid);
+    }
+  }
+  return l_blk;
+}
+
+constexpr bool kAt2Prefetch1 = false;
+constexpr bool kAt2Prefetch2 = false;   // pass-2 prefetch needs 64 + 64 (O row) + temporaries > 168 registers: spills
+
 constexpr int kAt2Threads = 192;
 constexpr int kAt2Stages = 2;
 struct Attn2Smem {
@@ -108,6 +220,9 @@ attention2_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat
       const int stage = j % kAt2Stages;
       mbar_wait(bar_p_full, (uint32_t)(j & 1));   // P_j written, so S_j has been read: the S buffer is free again
       tc_fence_after();
+      // S_{j+1} goes to the tensor pipe ahead of PV_j: the softmax warps start on block j+1 one MMA earlier, and PV_j
+      // runs underneath their pass 1 (they wait for its commit before they overwrite P)
+      if (j + 1 < nkb) issue_s(j + 1);
       if (elect_one()) {
         const uint32_t p_addr = smem_u32(smem + Attn2Smem::kP);
         const uint32_t v_addr = smem_u32(smem + Attn2Smem::kKV + stage * 2 * kAtTile + kAtTile);
@@ -123,8 +238,6 @@ attention2_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat
         umma_commit(bar_kv_empty + stage);
       }
       __syncwarp();
-      // S_{j+1} queues behind PV_j on the tensor pipe: its commit also tells the softmax warps that PV_j is done with P
-      if (j + 1 < nkb) issue_s(j + 1);
     }
   } else {
     // ---- softmax + accumulate: thread <-> query row ----
@@ -136,72 +249,22 @@ attention2_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat
 #pragma unroll
     for (int i = 0; i < 64; ++i) o[i] = 0.0f;
     float m_run = -INFINITY, l_run = 0.0f, alpha_prev = 0.0f;
-    uint8_t* p_row_base = smem + Attn2Smem::kP + row * 128;
+    const uint32_t p_row_s = smem_u32(smem + Attn2Smem::kP + row * 128);
     const int sw = row & 7;
     for (int j = 0; j < nkb; ++j) {
       mbar_wait(bar_s_full, (uint32_t)(j & 1));
       tc_fence_after();
       const uint32_t t_s = tmem_s + lane_sel;
       const int valid = S - j * 128;  // keys valid in this block (>= 128 except the last)
-      // pass 1: row max
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld32(t_s + c * 32, v);
-        tmem_ld_wait();
-        if (valid >= 128) {   // only the clip's last key block carries a mask
-          float m0 = -INFINITY, m1 = -INFINITY;
-#pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            m0 = fmaxf(m0, __uint_as_float(v[i]));
-            m1 = fmaxf(m1, __uint_as_float(v[i + 1]));
-          }
-          mx = fmaxf(mx, fmaxf(m0, m1));
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const float s = __uint_as_float(v[i]);
-            mx = fmaxf(mx, (c * 32 + i < valid) ? s : -INFINITY);
-          }
-        }
-      }
+      // pass 1: row max (only the clip's last key block carries a mask)
+      const float mx = valid >= 128 ? at2_pass1<false, kAt2Prefetch1>(t_s, valid) : at2_pass1<true, false>(t_s, valid);
       const float m_new = fmaxf(m_run, mx * c_scale);
       const float alpha = ex2_approx(m_run - m_new);
-      // pass 2: P = exp2(s*c - m), row sum, bf16 -> swizzled shared tile
-      float l_blk = 0.0f;
-      uint8_t* p_row = p_row_base;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld32(t_s + c * 32, v);
-        tmem_ld_wait();
-        float pv[32];
-        float la = 0.0f, lb = 0.0f;
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float p0 = ex2_approx(fmaf(__uint_as_float(v[i]), c_scale, -m_new));
-          float p1 = ex2_approx(fmaf(__uint_as_float(v[i + 1]), c_scale, -m_new));
-          if (valid < 128) {
-            if (c * 32 + i >= valid) p0 = 0.0f;
-            if (c * 32 + i + 1 >= valid) p1 = 0.0f;
-          }
-          pv[i] = p0;
-          pv[i + 1] = p1;
-          la += p0;
-          lb += p1;
-        }
-        l_blk += la + lb;
-        // 32 keys = 4 chunks of 16 bytes; key block c*32 lies in sub-tile c/2, chunk index (c&1)*4 + q
-        uint8_t* sub = p_row + (c >> 1) * kAtTile;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int chunk = ((c & 1) * 4 + q) ^ sw;
-          *reinterpret_cast<uint4*>(sub + chunk * 16) =
-              make_uint4(pack_bf16x2(pv[8 * q], pv[8 * q + 1]), pack_bf16x2(pv[8 * q + 2], pv[8 * q + 3]),
-                         pack_bf16x2(pv[8 * q + 4], pv[8 * q + 5]), pack_bf16x2(pv[8 * q + 6], pv[8 * q + 7]));
-        }
-      }
+      // pass 2: P = exp2(s*c - m), row sum, bf16 -> swizzled shared tile. S_j was issued AHEAD of PV_{j-1} (see the MMA
+      // warp), so PV_{j-1} may still be reading the P tile: its commit is awaited here, normally long since arrived
+      if (j >= 1) mbar_wait(bar_o_full + ((j - 1) & 1), (uint32_t)(((j - 1) >> 1) & 1));
+      const float l_blk = valid >= 128 ? at2_pass2<false, kAt2Prefetch2>(t_s, p_row_s, sw, c_scale, m_new, valid)
+                                       : at2_pass2<true, false>(t_s, p_row_s, sw, c_scale, m_new, valid);
       l_run = l_run * alpha + l_blk;
       m_run = m_new;
       fence_proxy_async();
