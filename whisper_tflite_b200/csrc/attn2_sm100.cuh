@@ -71,15 +71,17 @@ __device__ __forceinline__ float at2_pass1(uint32_t t_s, int valid) {
 // piece's row sum. 32 keys = 4 chunks of 16 bytes; key piece c lies in sub-tile c/2, chunk index (c&1)*4 + q.
 template <bool kMasked>
 __device__ __forceinline__ float at2_piece_exp(uint32_t (&v)[32], int c, uint32_t p_row_s, int sw, float c_scale, float m_new,
-                                               int valid) {
+                                               int valid, float& mx) {
   float la = 0.0f, lb = 0.0f;
 #pragma unroll
   for (int i = 0; i < 32; i += 2) {
     float p0 = ex2_approx(fmaf(__uint_as_float(v[i]), c_scale, -m_new));
     float p1 = ex2_approx(fmaf(__uint_as_float(v[i + 1]), c_scale, -m_new));
     if (kMasked) {
-      if (c * 32 + i >= valid) p0 = 0.0f;
-      if (c * 32 + i + 1 >= valid) p1 = 0.0f;
+      if (c * 32 + i >= valid) p0 = 0.0f; else mx = fmaxf(mx, __uint_as_float(v[i]));
+      if (c * 32 + i + 1 >= valid) p1 = 0.0f; else mx = fmaxf(mx, __uint_as_float(v[i + 1]));
+    } else {
+      mx = fmaxf(fmaxf(mx, __uint_as_float(v[i])), __uint_as_float(v[i + 1]));   // one FMNMX3
     }
     la += p0;
     lb += p1;
@@ -96,29 +98,31 @@ __device__ __forceinline__ float at2_piece_exp(uint32_t (&v)[32], int c, uint32_
   return la + lb;
 }
 template <bool kMasked, bool kPrefetch>
-__device__ __forceinline__ float at2_pass2(uint32_t t_s, uint32_t p_row_s, int sw, float c_scale, float m_new, int valid) {
+__device__ __forceinline__ float at2_pass2(uint32_t t_s, uint32_t p_row_s, int sw, float c_scale, float m_new, int valid,
+                                           float& mx) {
   float l_blk = 0.0f;
+  mx = -INFINITY;
   if (kPrefetch) {
     uint32_t va[32], vb[32];
     tmem_ld32(t_s, va);
     tmem_ld_wait();
     tmem_ld32(t_s + 32, vb);
-    l_blk = at2_piece_exp<kMasked>(va, 0, p_row_s, sw, c_scale, m_new, valid);
+    l_blk = at2_piece_exp<kMasked>(va, 0, p_row_s, sw, c_scale, m_new, valid, mx);
     tmem_ld_wait();
     tmem_ld32(t_s + 64, va);
-    l_blk += at2_piece_exp<kMasked>(vb, 1, p_row_s, sw, c_scale, m_new, valid);
+    l_blk += at2_piece_exp<kMasked>(vb, 1, p_row_s, sw, c_scale, m_new, valid, mx);
     tmem_ld_wait();
     tmem_ld32(t_s + 96, vb);
-    l_blk += at2_piece_exp<kMasked>(va, 2, p_row_s, sw, c_scale, m_new, valid);
+    l_blk += at2_piece_exp<kMasked>(va, 2, p_row_s, sw, c_scale, m_new, valid, mx);
     tmem_ld_wait();
-    l_blk += at2_piece_exp<kMasked>(vb, 3, p_row_s, sw, c_scale, m_new, valid);
+    l_blk += at2_piece_exp<kMasked>(vb, 3, p_row_s, sw, c_scale, m_new, valid, mx);
   } else {
 #pragma unroll 1
     for (int c = 0; c < 4; ++c) {
       uint32_t v[32];
       tmem_ld32(t_s + c * 32, v);
       tmem_ld_wait();
-      l_blk += at2_piece_exp<kMasked>(v, c, p_row_s, sw, c_scale, m_new, valid);
+      l_blk += at2_piece_exp<kMasked>(v, c, p_row_s, sw, c_scale, m_new, valid, mx);
     }
   }
   return l_blk;
@@ -248,7 +252,7 @@ attention2_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat
     float o[64];
 #pragma unroll
     for (int i = 0; i < 64; ++i) o[i] = 0.0f;
-    float m_run = -INFINITY, l_run = 0.0f, alpha_prev = 0.0f;
+    float m_run = -INFINITY, m_seen = -INFINITY, l_run = 0.0f, alpha_prev = 0.0f;
     const uint32_t p_row_s = smem_u32(smem + Attn2Smem::kP + row * 128);
     const int sw = row & 7;
     for (int j = 0; j < nkb; ++j) {
@@ -256,17 +260,30 @@ attention2_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat
       tc_fence_after();
       const uint32_t t_s = tmem_s + lane_sel;
       const int valid = S - j * 128;  // keys valid in this block (>= 128 except the last)
-      // pass 1: row max (only the clip's last key block carries a mask)
-      const float mx = valid >= 128 ? at2_pass1<false, kAt2Prefetch1>(t_s, valid) : at2_pass1<true, false>(t_s, valid);
-      const float m_new = fmaxf(m_run, mx * c_scale);
-      const float alpha = ex2_approx(m_run - m_new);
-      // pass 2: P = exp2(s*c - m), row sum, bf16 -> swizzled shared tile. S_j was issued AHEAD of PV_{j-1} (see the MMA
-      // warp), so PV_{j-1} may still be reading the P tile: its commit is awaited here, normally long since arrived
+      // Reference exponent of the block. Block 0: its exact row maximum (pass 1). Later blocks: the maximum of the blocks
+      // before it — P_j = exp2(s*c - m_ref) may then exceed 1, which is exact mathematics as long as nothing overflows;
+      // the block's own maximum comes out of the same pass and becomes the next reference. A row whose scores jump by
+      // more than 2^64 against everything seen before (never observed) redoes the block with its exact maximum.
+      float m_ref = m_seen;
+      if (j == 0) {
+        const float mx0 = valid >= 128 ? at2_pass1<false, kAt2Prefetch1>(t_s, valid) : at2_pass1<true, false>(t_s, valid);
+        m_ref = mx0 * c_scale;
+      }
+      // S_j was issued AHEAD of PV_{j-1} (see the MMA warp), so PV_{j-1} may still be reading the P tile: its commit is
+      // awaited here, normally long since arrived
       if (j >= 1) mbar_wait(bar_o_full + ((j - 1) & 1), (uint32_t)(((j - 1) >> 1) & 1));
-      const float l_blk = valid >= 128 ? at2_pass2<false, kAt2Prefetch2>(t_s, p_row_s, sw, c_scale, m_new, valid)
-                                       : at2_pass2<true, false>(t_s, p_row_s, sw, c_scale, m_new, valid);
+      // P = exp2(s*c - m_ref), row sum, block maximum, bf16 -> swizzled shared tile
+      float mx_blk;
+      float l_blk = valid >= 128 ? at2_pass2<false, kAt2Prefetch2>(t_s, p_row_s, sw, c_scale, m_ref, valid, mx_blk)
+                                 : at2_pass2<true, false>(t_s, p_row_s, sw, c_scale, m_ref, valid, mx_blk);
+      if (mx_blk * c_scale > m_ref + 64.0f) {
+        m_ref = mx_blk * c_scale;
+        l_blk = at2_pass2<true, false>(t_s, p_row_s, sw, c_scale, m_ref, valid, mx_blk);
+      }
+      const float alpha = ex2_approx(m_run - m_ref);   // previous reference -> this block's
       l_run = l_run * alpha + l_blk;
-      m_run = m_new;
+      m_run = m_ref;
+      m_seen = fmaxf(m_ref, mx_blk * c_scale);
       fence_proxy_async();
       tc_fence_before();
       __syncwarp();
