@@ -400,7 +400,7 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
         }
         if (p.flags & EPI_GELU) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = gelu_erf_fast(f[j]);
+          for (int j = 0; j < 32; ++j) f[j] = gelu_tanh_fit(f[j]);
         }
         if (p.flags & EPI_ADD) {
           // coalesced fetch of this warp's 32 rows x 32 cols of the addend through the scratch

@@ -40,6 +40,22 @@ __device__ __forceinline__ float gelu_erf_fast(float x) {
   return x * (x < 0.0f ? c : 1.0f - c);             // x Phi(x), no cancellation in the negative tail
 }
 
+// The GEMM epilogues' GELU: x Phi(x) with Phi(x) = 0.5 (1 + tanh(x (a + b x^2 + c x^4))), (a, b, c) a minimax fit of
+// the erf form itself (NOT the 0.044715 "tanh GELU": that one is 4.7e-4 off; this is 2.5e-5 off in exact arithmetic and
+// 3.0e-5 on the device with tanh.approx, tools/probes/gelu_probe.cu — a small fraction of a bf16 ulp of any output
+// that matters). x^2 is clamped at 49 because the quartic term turns the inner polynomial over beyond |x| = 7.25;
+// tanh.approx saturates to exactly +-1, so the tails are x and -0. 8 instructions, one MUFU (A&S 7.1.28 above: 17).
+__device__ __forceinline__ float gelu_tanh_fit(float x) {
+  const float x2 = fminf(x * x, 49.0f);
+  float p = fmaf(x2, -3.51516783e-4f, 0.037005646f);
+  p = fmaf(x2, p, 0.797507884f);
+  const float u = x * p;
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+  const float h = 0.5f * x;
+  return fmaf(h, t, h);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
