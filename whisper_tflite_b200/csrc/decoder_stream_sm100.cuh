@@ -232,8 +232,16 @@ __device__ __forceinline__ void ds_cluster_sync(uint8_t* smem, const DsParams& p
 // k phase (upw k blocks) -> warp -> unit, so a ring stage is one contiguous copy and warp w's share of it sits at
 // w * upw * 512.
 // ---------------------------------------------------------------------------------------------------
+// gpw = column groups per warp and round: 1 for the projections; 2 for the logits matrix, whose K = d gives 12 or 16 k
+// blocks — with one group per warp a stage is 8 x 6 units = 24 KB, with two it is 16 x 4 = the full 32 KB (the ring
+// keeps <= 4 copies in flight whatever their size, so stage bytes are stream rate). Groups i and i + 8 of a round
+// belong to warp i & 7; a warp's units of a stage are contiguous.
+__host__ __device__ inline int ds_round_prefix(int w, int na) {   // groups of the warps before w in a round of na groups
+  const int a = w < na ? w : na, b = na - 8 < w ? na - 8 : w;
+  return a + (b > 0 ? b : 0);
+}
 __global__ void ds_pack_weights_kernel(const __nv_bfloat16* __restrict__ W, const float* __restrict__ gamma,
-                                       uint4* __restrict__ out, int N, int K, int G) {
+                                       uint4* __restrict__ out, int N, int K, int G, int gpw) {
   const int n_groups = (N + 7) >> 3, kbK = K >> 5, gpc = (n_groups + G - 1) / G;
   const long long total = (long long)n_groups * kbK * 32;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
@@ -243,11 +251,12 @@ __global__ void ds_pack_weights_kernel(const __nv_bfloat16* __restrict__ W, cons
     const int kb = (int)(gk % kbK), g = (int)(gk / kbK);
     const int r = g / gpc, gl = g - r * gpc;
     const int ng_r = (n_groups - r * gpc < gpc) ? n_groups - r * gpc : gpc;
-    const int rho = gl >> 3, w = gl & 7;
-    const int nact = (ng_r - 8 * rho < 8) ? ng_r - 8 * rho : 8;
+    const int R = 8 * gpw, rho = gl / R, i = gl - rho * R, w = i & 7, j = i >> 3;
+    const int nact = (ng_r - R * rho < R) ? ng_r - R * rho : R;
     const int upw = ds_upw(kbK, nact);
     const int h = kb / upw, u = kb - h * upw;
-    const long long unit = (long long)r * gpc * kbK + (long long)rho * 8 * kbK + (long long)h * nact * upw + w * upw + u;
+    const long long unit = (long long)r * gpc * kbK + (long long)rho * R * kbK + (long long)h * nact * upw +
+                           (ds_round_prefix(w, nact) + j) * upw + u;
     const int n = g * 8 + (lane >> 2), k0 = kb * 32 + (lane & 3) * 8;
     uint32_t o[4] = {0u, 0u, 0u, 0u};
     if (n < N) {
@@ -535,36 +544,78 @@ __device__ __noinline__ DsRing ds_logits(uint8_t* smem, const DsParams& p, DsRin
   float* lg = p.step_logits ? p.step_logits + (size_t)step * p.step_logits_stride : nullptr;
   const bool r0 = g < B, r1 = g + 8 < B;
   unsigned long long best0 = 0ull, best1 = 0ull;
-  for (int rho = 0; rho * 8 < ng; ++rho) {
-    const bool active = rho * 8 + warp < ng;
-    const int n = (g0 + rho * 8 + warp) * 8 + 2 * t;
-    float2 bz = make_float2(0.0f, 0.0f);
-    if (active) bz = __ldg(reinterpret_cast<const float2*>(p.b_logits + n));  // padded to a multiple of 8 on the host
-    float acc[4];
-    {
-      const int nact = (ng - rho * 8 < 8) ? ng - rho * 8 : 8;
-      ds_mma_round<false>(smem, p, rg, ring, a_lane, as, nact == 8 ? upw_f : upw_l, nact == 8 ? kph_f : kph_l, nact, acc);
-    }
-    if (!active) continue;
-    const float v00 = acc[0] + bz.x, v01 = acc[1] + bz.y, v10 = acc[2] + bz.x, v11 = acc[3] + bz.y;
-    if (n < V) {
-      if (r0) best0 = u64_max(best0, pack_val_idx(v00, (unsigned)n));
-      if (r1) best1 = u64_max(best1, pack_val_idx(v10, (unsigned)n));
-    }
-    if (n + 1 < V) {
-      if (r0) best0 = u64_max(best0, pack_val_idx(v01, (unsigned)(n + 1)));
-      if (r1) best1 = u64_max(best1, pack_val_idx(v11, (unsigned)(n + 1)));
-    }
-    if (lg) {
-      if (r0) {
-        float* row = lg + (size_t)(p.clip0 + g) * V;
-        if (n < V) row[n] = v00;
-        if (n + 1 < V) row[n + 1] = v01;
+  uint64_t* full = ds_full(smem);
+  uint64_t* empty = ds_empty(smem);
+  constexpr int R = 2 * kDsConsWarps;   // 16 groups per round: warp w owns groups w and w + 8 (ds_pack_weights_kernel, gpw 2)
+  for (int rho = 0; rho * R < ng; ++rho) {
+    const int nact = (ng - rho * R < R) ? ng - rho * R : R;
+    const int upw = nact == R ? upw_f : upw_l, kph = nact == R ? kph_f : kph_l;
+    const int cnt = (warp < nact ? 1 : 0) + (warp + 8 < nact ? 1 : 0);       // this warp's groups in the round
+    const uint32_t w_off = (uint32_t)(ds_round_prefix(warp, nact) * upw) * kDsUnitBytes + lane * 16;
+    const int n0 = (g0 + rho * R + warp) * 8 + 2 * t, n1 = n0 + 64;          // first column of this lane in either group
+    float2 bz0 = make_float2(0.0f, 0.0f), bz1 = bz0;
+    if (cnt > 0) bz0 = __ldg(reinterpret_cast<const float2*>(p.b_logits + n0));  // padded to a multiple of 8 on the host
+    if (cnt > 1) bz1 = __ldg(reinterpret_cast<const float2*>(p.b_logits + n1));
+    float c0[4] = {0.0f, 0.0f, 0.0f, 0.0f}, c1[4] = {0.0f, 0.0f, 0.0f, 0.0f};   // group w: two chains over k
+    float e0[4] = {0.0f, 0.0f, 0.0f, 0.0f}, e1[4] = {0.0f, 0.0f, 0.0f, 0.0f};   // group w + 8
+    for (int h = 0; h < kph; ++h) {
+      mbar_wait(full + rg.slot, rg.par);
+      if (!(kDsProbe && (p.debug & 8))) {
+        const uint8_t* wp = ring + (size_t)rg.slot * kDsStageBytes + w_off;
+        const uint8_t* ap = a_lane + (size_t)(h * upw) * 64;
+        if (cnt > 1) {
+#pragma unroll 2
+          for (int u = 0; u < upw; ++u) {
+            const uint4 w0 = *reinterpret_cast<const uint4*>(wp + u * kDsUnitBytes);
+            const uint4 w1 = *reinterpret_cast<const uint4*>(wp + (upw + u) * kDsUnitBytes);
+            const uint4 lo = *reinterpret_cast<const uint4*>(ap + u * 64);
+            const uint4 hi = *reinterpret_cast<const uint4*>(ap + u * 64 + 8 * as);
+            mma_bf16_16816(c0, lo.x, hi.x, lo.y, hi.y, w0.x, w0.y);
+            mma_bf16_16816(e0, lo.x, hi.x, lo.y, hi.y, w1.x, w1.y);
+            mma_bf16_16816(c1, lo.z, hi.z, lo.w, hi.w, w0.z, w0.w);
+            mma_bf16_16816(e1, lo.z, hi.z, lo.w, hi.w, w1.z, w1.w);
+          }
+        } else if (cnt == 1) {
+#pragma unroll 2
+          for (int u = 0; u < upw; ++u) {
+            const uint4 w0 = *reinterpret_cast<const uint4*>(wp + u * kDsUnitBytes);
+            const uint4 lo = *reinterpret_cast<const uint4*>(ap + u * 64);
+            const uint4 hi = *reinterpret_cast<const uint4*>(ap + u * 64 + 8 * as);
+            mma_bf16_16816(c0, lo.x, hi.x, lo.y, hi.y, w0.x, w0.y);
+            mma_bf16_16816(c1, lo.z, hi.z, lo.w, hi.w, w0.z, w0.w);
+          }
+        }
       }
-      if (r1) {
-        float* row = lg + (size_t)(p.clip0 + g + 8) * V;
-        if (n < V) row[n] = v10;
-        if (n + 1 < V) row[n + 1] = v11;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty + rg.slot);
+      rg.advance();
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      if (j >= cnt) break;
+      const int n = j ? n1 : n0;
+      const float2 bz = j ? bz1 : bz0;
+      const float v00 = (j ? e0[0] + e1[0] : c0[0] + c1[0]) + bz.x, v01 = (j ? e0[1] + e1[1] : c0[1] + c1[1]) + bz.y;
+      const float v10 = (j ? e0[2] + e1[2] : c0[2] + c1[2]) + bz.x, v11 = (j ? e0[3] + e1[3] : c0[3] + c1[3]) + bz.y;
+      if (n < V) {
+        if (r0) best0 = u64_max(best0, pack_val_idx(v00, (unsigned)n));
+        if (r1) best1 = u64_max(best1, pack_val_idx(v10, (unsigned)n));
+      }
+      if (n + 1 < V) {
+        if (r0) best0 = u64_max(best0, pack_val_idx(v01, (unsigned)(n + 1)));
+        if (r1) best1 = u64_max(best1, pack_val_idx(v11, (unsigned)(n + 1)));
+      }
+      if (lg) {
+        if (r0) {
+          float* row = lg + (size_t)(p.clip0 + g) * V;
+          if (n < V) row[n] = v00;
+          if (n + 1 < V) row[n + 1] = v01;
+        }
+        if (r1) {
+          float* row = lg + (size_t)(p.clip0 + g + 8) * V;
+          if (n < V) row[n] = v10;
+          if (n + 1 < V) row[n + 1] = v11;
+        }
       }
     }
   }
@@ -867,12 +918,12 @@ struct DsProd {
     if (++slot == n_stages) { slot = 0; par ^= 1u; }
     return true;
   }
-  __device__ __forceinline__ bool weights(const uint4* base, int kind, uint64_t policy) {
+  __device__ __forceinline__ bool weights(const uint4* base, int kind, uint64_t policy, int R = kDsConsWarps) {
     const int ng = st->ng[kind], kbK = st->kbk[kind];
     const uint4* src = base + st->slice_unit0[kind] * 32;
-    for (int rho = 0; rho * 8 < ng; ++rho) {
-      const int nact = (ng - rho * 8 < 8) ? ng - rho * 8 : 8;
-      const int upw = nact == 8 ? st->upw_full[kind] : st->upw_last[kind], kph = kbK / upw;
+    for (int rho = 0; rho * R < ng; ++rho) {
+      const int nact = (ng - rho * R < R) ? ng - rho * R : R;
+      const int upw = nact == R ? st->upw_full[kind] : st->upw_last[kind], kph = kbK / upw;
       const uint32_t bytes = (uint32_t)(nact * upw * kDsUnitBytes);
       for (int h = 0; h < kph; ++h) {
         if (!issue(src, bytes, policy)) return false;
@@ -909,7 +960,7 @@ __device__ __noinline__ unsigned ds_producer(uint8_t* smem, const DsParams& p) {
       if (!pr.weights(L.w[DS_FC2], DS_FC2, pol_w)) return pr.n;
     }
     if (pos >= p.prompt_len - 1)
-      if (!pr.weights(p.w_logits, DS_LOGITS, pol_w)) return pr.n;
+      if (!pr.weights(p.w_logits, DS_LOGITS, pol_w, 2 * kDsConsWarps)) return pr.n;
   }
   return pr.n;
 }
@@ -949,8 +1000,9 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
       ng = ng < 0 ? 0 : (ng > gpc ? gpc : ng);
       st->ng[k] = ng;
       st->kbk[k] = kbK;
-      st->upw_full[k] = ds_upw(kbK, 8);
-      st->upw_last[k] = (ng & 7) ? ds_upw(kbK, ng & 7) : ds_upw(kbK, 8);
+      const int R = k == DS_LOGITS ? 2 * kDsConsWarps : kDsConsWarps;   // groups per round (ds_pack_weights_kernel's gpw)
+      st->upw_full[k] = ds_upw(kbK, R);
+      st->upw_last[k] = (ng % R) ? ds_upw(kbK, ng % R) : ds_upw(kbK, R);
       st->slice_unit0[k] = (long long)rank * gpc * kbK;
     }
     const int P = nb * p.H, base = P / G, rem = P - base * G;

@@ -865,7 +865,7 @@ int wt_engine::init_persistent_decoder() {
 int wt_engine::init_stream_weights() {
   const int d = dims.d_model, V = dims.n_vocab, G = dec_cluster;
   std::vector<wt::DsLayerDev> hl(dims.n_dec_layers);
-  auto pack = [&](const Lin& lin, const LNp* ln, const uint4** w_out, const float** b_out) -> int {
+  auto pack = [&](const Lin& lin, const LNp* ln, const uint4** w_out, const float** b_out, int gpw = 1) -> int {
     const int n_groups = (lin.N + 7) / 8, kbK = lin.K / 32;
     uint4* pw = nullptr;
     float* pb = nullptr;
@@ -873,7 +873,7 @@ int wt_engine::init_stream_weights() {
     WT_TRY(alloc(&pb, (size_t)n_groups * 8, true));
     const long long total = (long long)n_groups * kbK * 32;
     const int blocks = (int)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096);
-    wt::ds_pack_weights_kernel<<<blocks, 256, 0, stream>>>((const bf16*)lin.w, ln ? ln->g : nullptr, pw, lin.N, lin.K, G);
+    wt::ds_pack_weights_kernel<<<blocks, 256, 0, stream>>>((const bf16*)lin.w, ln ? ln->g : nullptr, pw, lin.N, lin.K, G, gpw);
     wt::ds_fold_bias_kernel<<<(lin.N * 32 + 255) / 256, 256, 0, stream>>>((const bf16*)lin.w, lin.b, ln ? ln->b : nullptr, pb, lin.N, lin.K);
     WT_CUDA_OK(cudaGetLastError());
     launches += 2;
@@ -898,7 +898,7 @@ int wt_engine::init_stream_weights() {
     emb.w = tok_emb; emb.b = nullptr; emb.N = V; emb.K = d;
     const uint4* w = nullptr;
     const float* b = nullptr;
-    WT_TRY(pack(emb, &dec_ln, &w, &b));
+    WT_TRY(pack(emb, &dec_ln, &w, &b, 2));   // two column groups per warp and round: 32 KB stages (ds_logits)
     ds_w_logits = const_cast<uint4*>(w);
     ds_b_logits = const_cast<float*>(b);
   }
