@@ -274,6 +274,7 @@ struct wt_engine {
   bool dec_persistent = false;
   int dec_cluster = 0, dec_group = 0, dec_groups_cap = 0, dec_active_clusters = 0;
   int dec_group_user = 0;  // wt_set_decoder_group (0 = automatic)
+  int attn_mode = -1;      // encoder attention kernel: -1 = not chosen yet, 0 = two CTAs per SM, 1 = one (WT_ATTN=1cta)
   int* gemm_sched = nullptr;  // {next tile, CTAs done} of the GEMM kernel's dynamic tile scheduler (self-resetting)
   wt::DecLayerDev* d_dec_layers = nullptr;
   float *pd_x = nullptr, *pd_qs = nullptr, *pd_att = nullptr, *pd_qx = nullptr, *pd_xpart = nullptr;
@@ -1123,7 +1124,11 @@ int wt_engine::encode(const float* mel, int n_clips, int mel_mem, float* states_
         WT_CUDA_OK(cudaFuncSetAttribute(wt::attention2_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::Attn2Smem::kTotal));
         attn_attr[device & 63] = true;
       }
-      static const bool one_cta = [] { const char* v = getenv("WT_ATTN"); return v && strcmp(v, "1cta") == 0; }();
+      if (attn_mode < 0) {  // WT_ATTN=1cta at engine creation time selects the one-CTA-per-SM kernel (attn_sm100.cuh)
+        const char* v = getenv("WT_ATTN");
+        attn_mode = (v && strcmp(v, "1cta") == 0) ? 1 : 0;
+      }
+      const bool one_cta = attn_mode == 1;
       pre_launch();
       if (one_cta) {
         wt::attention_sm100_kernel<<<dim3((S + 127) / 128, H, n_clips), wt::kAtThreads, wt::AttnSmem::kTotal, stream>>>(mq, (bf16*)att, S, H);
