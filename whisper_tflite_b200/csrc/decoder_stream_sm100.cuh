@@ -186,8 +186,7 @@ __device__ __forceinline__ void ds_pair_owner(const DsStream* st, int pr, int& c
 // release at cluster scope), and every consumer thread waits for its own CTA's mbarrier phase (acquire at cluster
 // scope). Data peers left in global memory (KV cache, qs) is read afterwards with L1-bypassing loads (__ldcg).
 __device__ __forceinline__ void ds_cluster_sync(uint8_t* smem, const DsParams& p, unsigned& cphase, int kind,
-                                                unsigned long long& tlast) {
-  const bool tr = p.trace != nullptr && threadIdx.x == 0;
+                                                unsigned long long& tlast, int G, bool tr) {
   const unsigned long long t_arr = tr ? dec_globaltimer() : 0ull;
   asm volatile("fence.acq_rel.cluster;" ::: "memory");
 #if DS_TRACE_FINE
@@ -195,7 +194,7 @@ __device__ __forceinline__ void ds_cluster_sync(uint8_t* smem, const DsParams& p
 #endif
   ds_cons_bar();
   const uint32_t local = smem_u32(ds_cbar(smem));
-  if (threadIdx.x < (unsigned)p.G) {
+  if (threadIdx.x < (unsigned)G) {
     const uint32_t remote = ds_mapa(local, (int)threadIdx.x);
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
   }
@@ -337,7 +336,6 @@ struct DsRing {
 
 // One 8-column group per warp and round, accumulated over kph ring stages of upw units (2 MMAs each, two independent
 // accumulator chains). Returns with the warp's 16 x 8 tile in acc (rows g / g+8, columns 2t, 2t+1 of the group).
-template <bool kEarly>
 __device__ __forceinline__ void ds_mma_round(uint8_t* smem, const DsParams& p, DsRing& rg, const uint8_t* ring,
                                              const uint8_t* a_lane, int as, int upw, int kph, int nact,
                                              float (&acc)[4]) {
@@ -346,36 +344,6 @@ __device__ __forceinline__ void ds_mma_round(uint8_t* smem, const DsParams& p, D
   uint64_t* full = ds_full(smem);
   uint64_t* empty = ds_empty(smem);
   float a0[4] = {0.0f, 0.0f, 0.0f, 0.0f}, a1[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-  if constexpr (kEarly) {
-  for (int h = 0; h < kph; ++h) {
-    mbar_wait(full + rg.slot, rg.par);
-    const uint8_t* wp = ring + (size_t)rg.slot * kDsStageBytes + (size_t)(warp * upw) * kDsUnitBytes + lane * 16;
-    const uint8_t* ap = a_lane + (size_t)(h * upw) * 64;
-    // weights leave the ring in groups of <= 6 units (24 registers); the stage goes back to the producer as soon as the
-    // last group is in registers, before its MMAs — the slot is held for the loads only
-    for (int u0 = 0; u0 < upw; u0 += 6) {
-      uint4 w[6];
-#pragma unroll
-      for (int u = 0; u < 6; ++u)
-        if (active && u0 + u < upw) w[u] = *reinterpret_cast<const uint4*>(wp + (u0 + u) * kDsUnitBytes);
-      if (u0 + 6 >= upw) {
-        __syncwarp();
-        if (lane == 0) mbar_arrive(empty + rg.slot);
-        rg.advance();
-      }
-      if (active) {
-#pragma unroll
-        for (int u = 0; u < 6; ++u)
-          if (u0 + u < upw) {
-            const uint4 lo = *reinterpret_cast<const uint4*>(ap + (u0 + u) * 64);
-            const uint4 hi = *reinterpret_cast<const uint4*>(ap + (u0 + u) * 64 + 8 * as);
-            mma_bf16_16816(a0, lo.x, hi.x, lo.y, hi.y, w[u].x, w[u].y);
-            mma_bf16_16816(a1, lo.z, hi.z, lo.w, hi.w, w[u].z, w[u].w);
-          }
-      }
-    }
-  }
-  } else {
   for (int h = 0; h < kph; ++h) {
     mbar_wait(full + rg.slot, rg.par);
     if (active && !(kDsProbe && (p.debug & 8))) {   // WT_DEC_DEBUG=8 (timing probe build): consume the weight stream without the MMAs
@@ -393,7 +361,6 @@ __device__ __forceinline__ void ds_mma_round(uint8_t* smem, const DsParams& p, D
     __syncwarp();
     if (lane == 0) mbar_arrive(empty + rg.slot);
     rg.advance();
-  }
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j) acc[j] = a0[j] + a1[j];
@@ -438,7 +405,7 @@ __device__ __forceinline__ void ds_gemm(uint8_t* smem, const DsParams& p, DsRing
     {
       const int nact = (ng - rho * 8 < 8) ? ng - rho * 8 : 8;
       const int upw = nact == 8 ? upw_f : upw_l;
-      ds_mma_round<false>(smem, p, rg, ring, a_lane, as, upw, nact == 8 ? kph_f : kph_l, nact, acc);
+      ds_mma_round(smem, p, rg, ring, a_lane, as, upw, nact == 8 ? kph_f : kph_l, nact, acc);
     }
     if (tr) { const unsigned long long t_ = dec_globaltimer(); atomicAdd(p.trace + 12, t_ - tm); tm = t_; }
     if (!active) continue;
@@ -1041,7 +1008,8 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
     if (tid == kDsConsThreads) issued = ds_producer(ds_smem, p);
   } else {
     const int B = p.n_clips;
-    unsigned long long tlast = (p.trace != nullptr && tid == 0) ? dec_globaltimer() : 0ull;
+    const bool tracing = p.trace != nullptr && tid == 0;   // registers: DsParams sits in shared memory (see DsRing)
+    unsigned long long tlast = tracing ? dec_globaltimer() : 0ull;
     unsigned cphase = 0;
     DsRing rg;
     rg.cons = 0; rg.slot = 0; rg.par = 0; rg.n_stages = p.n_stages;
@@ -1054,7 +1022,7 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
     }
     for (int pos = 0; pos <= p.max_total - 2; ++pos) {
       ds_embed(ds_smem, p, pos, xr);
-      ds_cluster_sync(ds_smem, p, cphase, 10, tlast);
+      ds_cluster_sync(ds_smem, p, cphase, 10, tlast, G, tracing);
       for (int l = 0; l < p.n_layers; ++l) {
         // phases 1..8: QKV, self-attention, out-proj, cross query, cross-attention, cross out-proj, fc1, fc2
 #pragma unroll 1
@@ -1067,12 +1035,12 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
             const int kind = ph == 1 ? DS_QKV : ph == 3 ? DS_OUT : ph == 4 ? DS_XQ : ph == 6 ? DS_XOUT : ph == 7 ? DS_FC1 : DS_FC2;
             ds_gemm(ds_smem, p, rg, kind, l, pos, xr);
           }
-          ds_cluster_sync(ds_smem, p, cphase, ph, tlast);
+          ds_cluster_sync(ds_smem, p, cphase, ph, tlast, G, tracing);
         }
       }
       if (pos >= p.prompt_len - 1) {
         rg = ds_logits(ds_smem, p, rg, pos);
-        ds_cluster_sync(ds_smem, p, cphase, 9, tlast);
+        ds_cluster_sync(ds_smem, p, cphase, 9, tlast, G, tracing);
         if (ds_finalize(ds_smem, p, pos) >= B) break;  // every clip has produced EOT (whisper.cpp:397-399, per clip)
       }
     }
