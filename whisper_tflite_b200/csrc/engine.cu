@@ -1154,7 +1154,16 @@ int wt_engine::encode(const float* mel, int n_clips, int mel_mem, float* states_
       next_kv_k = dec_persistent ? L.kvx : L.kx;
       next_kv_v = L.vx;
       next_kv_chunked = dec_persistent;
-      WT_TRY(linear(enc_out, M2, L.xkv, nullptr, wt::EPI_SPLIT_KV));
+      {
+        // batched per clip (S rows each; the last of a clip's 12 row tiles is padded by TMA): clip = batch, and with
+        // 128-key chunks the chunk index is the row tile — the scatter epilogue needs no division
+        const uint64_t ad[3] = {(uint64_t)L.xkv.K, (uint64_t)S, (uint64_t)n_clips};
+        const uint64_t as[2] = {(uint64_t)L.xkv.K * 2, (uint64_t)L.xkv.K * 2 * (uint64_t)S};
+        RowMap plain{0, M2, L.xkv.N};
+        stage = ST_XKV;
+        WT_TRY(gemm_bf16(enc_out, ad, as, S, n_clips, L.xkv, L.xkv.K, 1, 0, nullptr, nullptr, nullptr, plain,
+                         wt::EPI_SPLIT_KV, nullptr, plain, nullptr));
+      }
       gemm_stage = -1;
       continue;
     }

@@ -476,13 +476,21 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
             if (rb < p.rows_per_batch && col < p.N) {
               const uint4 val = *reinterpret_cast<const uint4*>(scr + rr * S::kScratchRowBytes + pc * 16);
               if (p.flags & EPI_SPLIT_KV) {
-                const int mm = batch * p.rows_per_batch + rb;
-                const int clip = mm / p.kv_S, sq = mm - clip * p.kv_S;
+                int clip = batch, sq = rb;     // launched per clip (rows_per_batch == kv_S): no division
+                if (p.rows_per_batch != p.kv_S) {
+                  const int mm = batch * p.rows_per_batch + rb;
+                  clip = mm / p.kv_S;
+                  sq = mm - clip * p.kv_S;
+                }
                 const int dm = p.kv_H * 64;
                 const int which = col >= dm, cc = which ? col - dm : col;
                 __nv_bfloat16* dst;
                 if (p.kv_chunk > 0) {
-                  const int ch = sq / p.kv_chunk, kin = sq - ch * p.kv_chunk;
+                  int ch = sq >> 7, kin = sq & 127;
+                  if (p.kv_chunk != 128) {
+                    ch = sq / p.kv_chunk;
+                    kin = sq - ch * p.kv_chunk;
+                  }
                   // 16-byte segments of a key's 128-byte row are XOR-swizzled by key & 7: the decoder reads the chunk
                   // with ldmatrix straight out of the bulk-copied stage (decoder_stream_sm100.cuh: ds_cross_attn)
                   dst = p.kv_k + ((((size_t)(clip * p.kv_H + (cc >> 6)) * p.kv_cpp + ch) * 2 + which) * p.kv_chunk + kin) * 64 +
