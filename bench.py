@@ -392,7 +392,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--dec-group", type=int, default=16,
                     help="clips per decoder cluster when engines > 1 (64 clips: 16 -> 4 clusters = 64 SMs, 13 -> 5 = 80 SMs)")
-    ap.add_argument("--engines", type=int, default=2, help="engines per GPU that batches alternate between (1 = no pipelining)")
+    ap.add_argument("--engines", type=int, default=3, help="engines per GPU that batches alternate between (1 = no pipelining)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
