@@ -20,6 +20,12 @@ import sys
 import threading
 import time
 
+if "reference" in sys.argv and int(os.environ.get("RANK", "0")) == 0:
+    # the reference arm times the CPU path with every host thread: torchrun presets OMP_NUM_THREADS=1 for its workers,
+    # which the BLAS behind numpy reads once, at import
+    for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[_v] = str(os.cpu_count() or 1)
+
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
