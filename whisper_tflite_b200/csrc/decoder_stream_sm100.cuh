@@ -289,41 +289,51 @@ __global__ void ds_fold_bias_kernel(const __nv_bfloat16* __restrict__ W, const f
 
 
 // ---------------------------------------------------------------------------------------------------
-// LayerNorm (gain/bias folded into the packed weights) of the residual copy sX -> MMA operand tile sA: one warp per
-// row, shared memory to shared memory, no global access.
+// LayerNorm (gain/bias folded into the packed weights) of the residual copy sX -> MMA operand tile sA, shared memory to
+// shared memory. Half a warp per row, so a warp's two rows reduce side by side (two passes of 4 shuffle steps instead
+// of 2 x 2 x 5 in sequence: the phase starts behind this chain); the row is re-read from shared memory in each pass
+// instead of being held in registers. d is a multiple of 128 (16 lanes x 8 bf16).
 // ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float ds_half_sum(float v) {
+#pragma unroll
+  for (int o = 8; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
 __device__ __forceinline__ void ds_stage_norm(uint8_t* smem, int n_clips, int d) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint8_t* sX = smem + DsSmem::kX;
-  uint8_t* sA = smem + DsSmem::a_off(d);
-  const int xs = DsSmem::x_stride(d), as = DsSmem::a_stride(d);
-  const int per = d >> 6;  // bf16 pairs per lane
-  for (int r = warp; r < n_clips; r += kDsConsWarps) {
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(sX + (size_t)r * xs);
-    uint32_t* dst = reinterpret_cast<uint32_t*>(sA + (size_t)r * as);
-    float2 v[kDecMaxD / 64];
-    float s = 0.0f;
+  const int r = warp * 2 + (lane >> 4), l16 = lane & 15;    // kDsRows == 2 * kDsConsWarps rows, one pass
+  static_assert(kDsRows == 2 * kDsConsWarps, "two rows per consumer warp");
+  const bool on = r < n_clips;
+  const uint4* src = reinterpret_cast<const uint4*>(smem + DsSmem::kX + (size_t)r * DsSmem::x_stride(d)) + l16;
+  uint4* dst = reinterpret_cast<uint4*>(smem + DsSmem::a_off(d) + (size_t)r * DsSmem::a_stride(d)) + l16;
+  const int nv = d >> 7;   // 16-byte pieces per lane
+  float s = 0.0f;
+  if (on)
+    for (int i = 0; i < nv; ++i) {
+      float f[8];
+      bf16x8_to_f32(src[i * 16], f);
+      s += ((f[0] + f[1]) + (f[2] + f[3])) + ((f[4] + f[5]) + (f[6] + f[7]));
+    }
+  const float mean = ds_half_sum(s) / (float)d;
+  float q = 0.0f;
+  if (on)
+    for (int i = 0; i < nv; ++i) {
+      float f[8];
+      bf16x8_to_f32(src[i * 16], f);
 #pragma unroll
-    for (int i = 0; i < kDecMaxD / 64; ++i)
-      if (i < per) {
-        const uint32_t w = src[i * 32 + lane];
-        v[i] = make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
-        s += v[i].x + v[i].y;
+      for (int j = 0; j < 8; ++j) {
+        const float c = f[j] - mean;
+        q = fmaf(c, c, q);
       }
-    const float mean = warp_sum(s) / (float)d;
-    float q = 0.0f;
-#pragma unroll
-    for (int i = 0; i < kDecMaxD / 64; ++i)
-      if (i < per) {
-        v[i].x -= mean;
-        v[i].y -= mean;
-        q += v[i].x * v[i].x + v[i].y * v[i].y;
-      }
-    const float rstd = rsqrtf(warp_sum(q) / (float)d + 1e-5f);
-#pragma unroll
-    for (int i = 0; i < kDecMaxD / 64; ++i)
-      if (i < per) dst[i * 32 + lane] = dec_pack2(v[i].x * rstd, v[i].y * rstd);
-  }
+    }
+  const float rstd = rsqrtf(ds_half_sum(q) / (float)d + 1e-5f);
+  if (on)
+    for (int i = 0; i < nv; ++i) {
+      float f[8];
+      bf16x8_to_f32(src[i * 16], f);
+      dst[i * 16] = make_uint4(dec_pack2((f[0] - mean) * rstd, (f[1] - mean) * rstd), dec_pack2((f[2] - mean) * rstd, (f[3] - mean) * rstd),
+                               dec_pack2((f[4] - mean) * rstd, (f[5] - mean) * rstd), dec_pack2((f[6] - mean) * rstd, (f[7] - mean) * rstd));
+    }
 }
 
 // ring position of the consumers (uniform over the consumer threads)
