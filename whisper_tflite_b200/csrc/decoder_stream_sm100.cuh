@@ -717,8 +717,9 @@ __device__ __forceinline__ void ds_mma_row0(float& c0, float& c1, uint32_t a0, u
 // One softmax step of a warp over its 16-key slabs of NCH consecutive chunks (ring stages) of a pair: with NCH = 2 the
 // two score chains, one max reduction and one rescale cover 32 keys, which halves the dependent latency per chunk —
 // the phase is bound by that chain, not by issue slots or the stream (WT_DEC_DEBUG=4 measures the stream alone).
-// (NCH = 2 measured slower on B200: two ring stages held at once and register spills around the call sites.)
-constexpr int kDsXaChunksPerStep = 1;
+// (NCH = 2 is only a win without spills: 5.17 vs 5.09 ms per launch's cross-attention while the kernel sat at the
+// 168-register cap, 3.58 vs 3.70 ms once the LayerNorm staging stopped holding rows in registers.)
+constexpr int kDsXaChunksPerStep = 2;
 template <int NCH>
 __device__ __forceinline__ void ds_xa_step(const DsParams& p, DsRing& rg, uint32_t ring, uint64_t* full, uint64_t* empty,
                                            uint32_t k_off, uint32_t v_off, const uint32_t (&qa)[4][2], int n_keys_last,
@@ -841,8 +842,12 @@ __device__ __noinline__ DsRing ds_cross_attn(uint8_t* smem, const DsParams& p, D
 #pragma unroll
     for (int i = 0; i < 8; ++i) o[i][0] = o[i][1] = 0.0f;
     const int n_last = S - (cpp - 1) * kXaChunk;   // keys in the pair's last chunk
-    for (int c = 0; c < cpp; ++c)
-      ds_xa_step<kDsXaChunksPerStep>(p, rg, ring, full, empty, k_off, v_off, qa, c + 1 == cpp ? n_last : kXaChunk, m, lsum, o);
+    int c = 0;
+    if (kDsXaChunksPerStep == 2)
+      for (; c + 2 <= cpp; c += 2)
+        ds_xa_step<2>(p, rg, ring, full, empty, k_off, v_off, qa, c + 2 == cpp ? n_last : kXaChunk, m, lsum, o);
+    for (; c < cpp; ++c)
+      ds_xa_step<1>(p, rg, ring, full, empty, k_off, v_off, qa, c + 1 == cpp ? n_last : kXaChunk, m, lsum, o);
     lsum += __shfl_xor_sync(0xffffffffu, lsum, 1);
     lsum += __shfl_xor_sync(0xffffffffu, lsum, 2);
     ds_cons_bar();  // s_misc free (previous pair's merge done)
