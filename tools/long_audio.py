@@ -58,8 +58,14 @@ total = n_win * repeat
 dt, ids, lens = run(total)
 same = all(np.array_equal(ids[r * n_win:(r + 1) * n_win], ids1) and np.array_equal(lens[r * n_win:(r + 1) * n_win], lens1)
            for r in range(repeat))
+rep = ids.reshape(repeat, n_win, -1)
+n_diff = int((rep != ids1[None]).any(axis=2).sum())
+# batches of 64 over a period of 120 windows: repeats r and r + 8 see the same batch composition and batch positions
+period = 8
+same_align = bool(repeat <= period or np.array_equal(rep[:repeat - period], rep[period:]))
 line = {"workload": f"the same hour x{repeat}", "windows": total, "seconds": round(dt, 5), "rtfx": round(total * 30.0 / dt, 1),
-        "ids_identical_to_single_pass": bool(same)}
+        "ids_identical_to_single_pass": bool(same), "windows_differing_from_single_pass": n_diff,
+        "identical_at_equal_batch_alignment": same_align}
 print(json.dumps(line), flush=True)
 if out:
     out.write(json.dumps(line) + "\n")
