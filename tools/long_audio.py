@@ -2,7 +2,7 @@
 -> token ids, through the PCM-in / ids-out call (wt_transcribe_tokens, the Monolith path: whisper.cpp:692-738) with HOST
 buffers, batches of <= 64 windows on an EnginePool; then the same stream repeated x32 (3 840 windows) so that the work
 is long enough to read a rate from. Wall clock around the calls (they return synchronised). One JSON line per run.
-usage: python tools/long_audio.py [out.jsonl] [repeat=32]"""
+usage: python tools/long_audio.py [out.jsonl] [repeat=32] [engines=3]"""
 import json
 import os
 import sys
@@ -27,7 +27,8 @@ assert n_win == 120
 ring = torch.empty(n_win + B, shard.WINDOW, dtype=torch.float32).pin_memory()
 ring[:n_win] = torch.from_numpy(windows)
 ring[n_win:] = ring[:B]
-pool = capi.EnginePool(bench.ensure_weights("tiny"), n_engines=3, max_batch=B)
+n_eng = int(sys.argv[3]) if len(sys.argv) > 3 else 3
+pool = capi.EnginePool(bench.ensure_weights("tiny"), n_engines=n_eng, max_batch=B)
 
 
 def run(total):
@@ -49,7 +50,7 @@ def run(total):
 
 run(n_win)                                                  # warm-up
 dt1, ids1, lens1 = run(n_win)
-line = {"workload": "1 h of audio = 120 windows, host PCM in, ids out, 3 engines", "windows": n_win, "seconds": round(dt1, 5),
+line = {"workload": "1 h of audio = 120 windows, host PCM in, ids out, %d engines" % n_eng, "windows": n_win, "seconds": round(dt1, 5),
         "rtfx": round(n_win * 30.0 / dt1, 1), "lens_ok": bool((lens1 >= 5).all())}
 print(json.dumps(line), flush=True)
 if out:
