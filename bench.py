@@ -217,18 +217,21 @@ def run_gpu(args):
     sets = [synth.synth_pcm(B, seed=1000 * s_ + rank) for s_ in range(n_sets)]
     d_sets = [torch.from_numpy(p_).cuda() for p_ in sets]
     h_sets = [torch.from_numpy(p_).pin_memory() for p_ in sets]
-    d_ids = [torch.empty(B, capi.MAX_TOKENS, dtype=torch.int32, device="cuda") for _ in range(n_eng)]
-    d_lens = [torch.empty(B, dtype=torch.int32, device="cuda") for _ in range(n_eng)]
-    h_ids = [torch.empty(B, capi.MAX_TOKENS, dtype=torch.int32).pin_memory() for _ in range(n_eng)]
-    h_lens = [torch.empty(B, dtype=torch.int32).pin_memory() for _ in range(n_eng)]
+    # one result buffer per timed step (not per engine): every step's ids are compared with a single-engine pass
+    # over the same PCM set after the timed region
+    n_out = max(args.steps, args.warmup * n_eng, n_eng, 3)
+    d_ids = [torch.empty(B, capi.MAX_TOKENS, dtype=torch.int32, device="cuda") for _ in range(n_out)]
+    d_lens = [torch.empty(B, dtype=torch.int32, device="cuda") for _ in range(n_out)]
+    h_ids = [torch.empty(B, capi.MAX_TOKENS, dtype=torch.int32).pin_memory() for _ in range(n_out)]
+    h_lens = [torch.empty(B, dtype=torch.int32).pin_memory() for _ in range(n_out)]
 
     def step_dev(i):
         j = i % n_eng
-        engs[j].transcribe_tokens(d_sets[i % n_sets], ids_out=d_ids[j], lens_out=d_lens[j])  # asynchronous enqueue
+        engs[j].transcribe_tokens(d_sets[i % n_sets], ids_out=d_ids[i % n_out], lens_out=d_lens[i % n_out])  # asynchronous enqueue
 
     def step_e2e(i):
         j = i % n_eng
-        engs[j].transcribe_tokens(h_sets[i % n_sets], ids_out=h_ids[j], lens_out=h_lens[j])  # H2D + compute + D2H, returns synced
+        engs[j].transcribe_tokens(h_sets[i % n_sets], ids_out=h_ids[i % n_out], lens_out=h_lens[i % n_out])  # H2D + compute + D2H, returns synced
 
     from concurrent.futures import ThreadPoolExecutor
     workers = [ThreadPoolExecutor(1) for _ in range(n_eng)]  # one host thread per engine (the C call releases the GIL)
@@ -276,14 +279,32 @@ def run_gpu(args):
     # per-stage device times (CUDA events around every launch, same stream) for the roofline
     prof_steps = max(1, min(args.steps, 3))
     torch.cuda.synchronize()
+    p_ids = torch.empty(B, capi.MAX_TOKENS, dtype=torch.int32, device="cuda")
+    p_lens = torch.empty(B, dtype=torch.int32, device="cuda")
     eng.profile(True)
     for i in range(prof_steps):   # engine 0 alone, steps back to back: per-kernel durations without co-running kernels
-        eng.transcribe_tokens(d_sets[i % n_sets], ids_out=d_ids[0], lens_out=d_lens[0])
+        eng.transcribe_tokens(d_sets[i % n_sets], ids_out=p_ids, lens_out=p_lens)
     stages = eng.profile_read()
     eng.profile(False)
-    # result sanity: every clip produced the prompt + generated tokens
+    # result check (outside the timed region): the ids of EVERY timed step, device-resident and end-to-end, against a
+    # single-engine pass over the same PCM set — a window maps to one id list whatever engine, stream or co-running
+    # kernels it met (whisper.cpp:367-400); plus the decoded lengths (the loop exits early on EOT, so RTFx depends on them)
     torch.cuda.synchronize()
-    lens_ok = all(bool(((dl >= 5) & (dl <= capi.MAX_TOKENS)).all().item()) for dl in d_lens)
+    ref = []
+    for k in range(n_sets):
+        ri = torch.empty(B, capi.MAX_TOKENS, dtype=torch.int32, device="cuda")
+        rl = torch.empty(B, dtype=torch.int32, device="cuda")
+        eng.transcribe_tokens(d_sets[k], ids_out=ri, lens_out=rl)
+        torch.cuda.synchronize()
+        ref.append((ri.cpu(), rl.cpu()))
+    mism = 0
+    for i in range(args.steps):
+        ri, rl = ref[i % n_sets]
+        mism += int((d_ids[i % n_out].cpu() != ri).any(dim=1).sum()) + int((h_ids[i % n_out] != ri).any(dim=1).sum())
+        mism += int((d_lens[i % n_out].cpu() != rl).sum()) + int((h_lens[i % n_out] != rl).sum())
+    all_lens = torch.cat([rl for _, rl in ref]).float()
+    lens_ok = bool(((all_lens >= 5) & (all_lens <= capi.MAX_TOKENS)).all().item())
+    results_ok = lens_ok and mism == 0
 
     if rank == 0:
         pk = peaks()
@@ -368,7 +389,10 @@ def run_gpu(args):
                     "d2h_bytes_per_step": int(world * B * (capi.MAX_TOKENS + 1) * 4)},
             "roofline": roofline,
             "stages_ms_per_step": {k: round(v["ms_per_step"], 4) for k, v in per_stage.items()},
-            "stages_total_ms": round(total_prof, 3), "results_ok": lens_ok,
+            "stages_total_ms": round(total_prof, 3), "results_ok": results_ok,
+            "results_check": {"what": "ids and lens of every timed step (device-resident and e2e) == single-engine pass over the same PCM set",
+                              "clips_differing": mism, "steps_checked": 2 * args.steps,
+                              "tokens_per_clip": {"mean": float(all_lens.mean()), "min": int(all_lens.min()), "max": int(all_lens.max())}},
         }
         if world == 1 and not args.no_cpu_baseline:
             from oracle import mel as omel

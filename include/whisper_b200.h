@@ -135,6 +135,37 @@ WT_API const char* wt_version(void);
 WT_API int wt_debug_gemm_bf16(void* cuda_stream, const void* A, const void* W, const float* bias, void* C, int M, int N,
                               int K, int flags);
 
+/* Kernel-level test hooks (tests/test_gpu_kernels.py compares them with fp32 torch references).
+ * wt_debug_gemm_ex: the tcgen05 GEMM with every addressing / epilogue feature the engine uses. A is a bf16 tensor
+ * {a_dims[0] inner, a_dims[1] rows, a_dims[2] batches} with byte strides a_strides[0..1]; K is walked as `taps` groups
+ * (tap t reads A at column tap_c0[t], row offset tap_row[t]; W column t*tap_k) — taps = 1 is a plain GEMM, 3 the k=3
+ * convolutions. Output row m lives at C + (m / c_rows) * c_batch_stride + (m % c_rows) * c_row_stride (elements);
+ * the addend (flags & 4) likewise. flags: 1 bias, 2 GELU, 4 add, 16 f32 output, 32 fused (max, last index) into
+ * argmax_part [M][ceil(N/bn)] u64, 64 K/V scatter into kv_out (kv_chunked != 0: the decoder's chunk stream with
+ * XOR-swizzled 16-byte segments; else [clip][H][kv_S][64] K into kv_out, V into kv_out_v). All pointers device. */
+typedef struct wt_debug_gemm_args {
+  int32_t struct_size;
+  const void* A; uint64_t a_dims[3]; uint64_t a_strides[2];
+  int32_t rows_per_batch, n_batches;
+  const void* W; const float* bias; int32_t N, K_total;
+  int32_t taps, tap_k, tap_c0[3], tap_row[3];
+  void* C; int64_t c_batch_stride; int32_t c_rows, c_row_stride;
+  const void* addend; int64_t add_batch_stride; int32_t add_rows, add_row_stride;
+  uint64_t* argmax_part;
+  void *kv_out, *kv_out_v; int32_t kv_S, kv_H, kv_chunked;
+  int32_t flags, force_bn;
+} wt_debug_gemm_args;
+WT_API int wt_debug_gemm_ex(void* cuda_stream, const wt_debug_gemm_args* a);
+
+/* The encoder attention kernel alone: qkv [n_clips][S][3*H*64] bf16 (q | k | v) -> out [n_clips][S][H*64] bf16. */
+WT_API int wt_debug_attention_bf16(void* cuda_stream, const void* qkv, void* out, int n_clips, int S, int H);
+
+/* Debug / test hook: 64-bit order-independent digest of a device-resident buffer as the last call on this engine left
+ * it, over the first n_clips clips. what: "mel_raw", "mel_tm", "conv1", "x", "qkv", "att", "hidden", "enc_out",
+ * "cross_kv<layer>", "tokens". Equal bytes give equal digests: the bitwise-reproducibility tests compare these across
+ * repeats and engines (a window must map to ONE id list: whisper.cpp:367-400). Synchronises the engine's stream. */
+WT_API int wt_debug_hash(wt_engine* e, const char* what, int n_clips, uint64_t* out);
+
 /* Engines created with WT_DEC_TRACE=1 in the environment: nanoseconds per phase kind of the persistent decoder as
  * seen by CTA 0, accumulated over launches. out32[k] = phase k total (0 init, 1..8 the layer phases, 9 logits,
  * 10 finalize+embed), out32[16+k] = the part of it spent waiting in the grid barrier. */

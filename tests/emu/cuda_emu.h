@@ -169,6 +169,9 @@ static inline float atomicAdd(float* a, float v) {
   std::memcpy(&f, &old, 4);
   return f;
 }
+static inline unsigned long long atomicAdd(unsigned long long* a, unsigned long long v) {
+  return reinterpret_cast<std::atomic<unsigned long long>*>(a)->fetch_add(v);
+}
 static inline unsigned long long atomicMax(unsigned long long* a, unsigned long long v) {
   auto* p = reinterpret_cast<std::atomic<unsigned long long>*>(a);
   unsigned long long old = p->load();

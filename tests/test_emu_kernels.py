@@ -180,20 +180,27 @@ def test_decode_attention_self_and_cross(simt):
 
 
 def test_argmax_last_tie_and_eot_state(simt):
-    B, V = 3, 1000
+    """whisper.cpp:346-361: `>=` scan from max_value = row[0]: last maximal index; a NaN at index > 0 never wins, a NaN
+    at index 0 is never replaced (the oracle's argmax_last restates the same scan)."""
+    B, V = 4, 1000
     logits = np.random.RandomState(5).randn(B, V).astype(np.float32)
     logits[0, 10] = logits[0, 900] = 9.0  # tie -> last index
-    logits[1, 0] = np.nan
+    logits[1, 1] = np.nan
     logits[1, 77] = 5.0
     logits[2, 500] = 8.0
+    logits[3, 0] = np.nan                 # NaN first: index 0 survives every comparison
+    logits[3, 400] = 9.0
     tokens = np.full((B, 31), -1, np.int32)
     lens = np.full(B, 4, np.int32)
-    done = np.array([0, 0, 1], np.int32)
+    done = np.array([0, 0, 1, 0], np.int32)
     I = lambda a: a.ctypes.data_as(ip)
     simt.emu_argmax_append(P(logits), V, I(tokens), 31, I(lens), I(done), 3, 77, B)
     assert tokens[0, 4] == 900 and lens[0] == 5 and done[0] == 0
-    assert tokens[1, 4] == 77 and done[1] == 1  # NaN never wins; 77 == eot -> done
+    assert tokens[1, 4] == 77 and done[1] == 1  # NaN at index 1 never wins; 77 == eot -> done
     assert tokens[2, 4] == -1 and lens[2] == 4  # finished clip untouched
+    assert tokens[3, 4] == 0 and lens[3] == 5
+    for b in (0, 1, 3):
+        assert model_ref.argmax_last(logits[b]) == tokens[b, 4]
 
 
 def test_mel_to_time_major(simt):

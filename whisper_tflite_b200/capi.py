@@ -28,7 +28,7 @@ EXPORTED = [
     "wt_synchronize", "wt_log_mel", "wt_encode", "wt_decode_greedy", "wt_transcribe_tokens",
     "wt_get_step_logits", "wt_launch_count", "wt_last_error", "wt_version", "wt_debug_gemm_bf16",
     "wt_profile_enable", "wt_profile_read", "wt_stage_count", "wt_stage_name", "wt_debug_decoder_trace",
-    "wt_set_decoder_group",
+    "wt_set_decoder_group", "wt_debug_hash", "wt_debug_gemm_ex", "wt_debug_attention_bf16",
 ]
 
 
@@ -208,6 +208,12 @@ class Engine:
         _check(self.lib.wt_debug_decoder_trace(self.h, buf, int(reset)))
         return {n: (buf[i] / 1e3, buf[16 + i] / 1e3) for i, n in enumerate(names)}
 
+    def debug_hash(self, what: str, n_clips: int) -> int:
+        """64-bit digest of a resident buffer ("enc_out", "cross_kv0", "x", "qkv", ... see whisper_b200.h)."""
+        h = ctypes.c_uint64(0)
+        _check(self.lib.wt_debug_hash(self.h, what.encode(), int(n_clips), ctypes.byref(h)))
+        return int(h.value)
+
     def step_logits(self, step: int, n_clips: int) -> np.ndarray:
         out = np.empty((n_clips, self.dims.n_vocab), dtype=np.float32)
         _check(self.lib.wt_get_step_logits(self.h, step, n_clips, ctypes.c_void_p(out.ctypes.data), WT_HOST))
@@ -223,6 +229,52 @@ def debug_gemm_bf16(a, w, bias, c, flags: int = 0, stream: int = 0):
                                   ctypes.c_void_p(bias.data_ptr()) if bias is not None else None,
                                   ctypes.c_void_p(c.data_ptr()), M, N, K, flags | (1 if bias is not None else 0)))
     return c
+
+
+EPI_BIAS, EPI_GELU, EPI_ADD, EPI_OUT_F32, EPI_ARGMAX, EPI_SPLIT_KV = 1, 2, 4, 16, 32, 64
+
+
+class WtDebugGemmArgs(ctypes.Structure):
+    _fields_ = [("struct_size", ctypes.c_int32),
+                ("A", ctypes.c_void_p), ("a_dims", ctypes.c_uint64 * 3), ("a_strides", ctypes.c_uint64 * 2),
+                ("rows_per_batch", ctypes.c_int32), ("n_batches", ctypes.c_int32),
+                ("W", ctypes.c_void_p), ("bias", ctypes.c_void_p), ("N", ctypes.c_int32), ("K_total", ctypes.c_int32),
+                ("taps", ctypes.c_int32), ("tap_k", ctypes.c_int32), ("tap_c0", ctypes.c_int32 * 3),
+                ("tap_row", ctypes.c_int32 * 3),
+                ("C", ctypes.c_void_p), ("c_batch_stride", ctypes.c_int64), ("c_rows", ctypes.c_int32),
+                ("c_row_stride", ctypes.c_int32),
+                ("addend", ctypes.c_void_p), ("add_batch_stride", ctypes.c_int64), ("add_rows", ctypes.c_int32),
+                ("add_row_stride", ctypes.c_int32),
+                ("argmax_part", ctypes.c_void_p),
+                ("kv_out", ctypes.c_void_p), ("kv_out_v", ctypes.c_void_p), ("kv_S", ctypes.c_int32),
+                ("kv_H", ctypes.c_int32), ("kv_chunked", ctypes.c_int32),
+                ("flags", ctypes.c_int32), ("force_bn", ctypes.c_int32)]
+
+
+def debug_gemm_ex(stream: int = 0, **kw):
+    """wt_debug_gemm_ex with keyword fields of wt_debug_gemm_args; torch CUDA tensors are passed by data_ptr()."""
+    a = WtDebugGemmArgs()
+    a.struct_size = ctypes.sizeof(WtDebugGemmArgs)
+    keep = []
+    for k, v in kw.items():
+        if hasattr(v, "data_ptr"):
+            keep.append(v)
+            v = v.data_ptr()
+        if isinstance(v, (list, tuple)):
+            arr = getattr(a, k)
+            for i, x in enumerate(v):
+                arr[i] = int(x)
+        else:
+            setattr(a, k, v)
+    _check(load_library().wt_debug_gemm_ex(ctypes.c_void_p(stream), ctypes.byref(a)))
+
+
+def debug_attention_bf16(qkv, out, n_heads: int, stream: int = 0):
+    """attention2_sm100_kernel on qkv [B][S][3*H*64] -> out [B][S][H*64] (torch CUDA bf16 tensors)."""
+    B, S, _ = qkv.shape
+    _check(load_library().wt_debug_attention_bf16(ctypes.c_void_p(stream), ctypes.c_void_p(qkv.data_ptr()),
+                                                  ctypes.c_void_p(out.data_ptr()), B, S, n_heads))
+    return out
 
 
 class EnginePool:

@@ -26,7 +26,7 @@
 #ifndef DS_TRACE_FINE
 #define DS_TRACE_FINE 0
 #endif
-#include "decoder_sm100.cuh"  // shared small helpers (mma wrapper, bf16 unpack, ex2, globaltimer, cluster ids)
+#include "dec_common.cuh"  // shared small helpers (mma wrapper, bf16 unpack, ex2, globaltimer, cluster ids)
 
 namespace wt {
 

@@ -24,7 +24,6 @@
 #include "../../include/whisper_b200.h"
 #include "attn_sm100.cuh"
 #include "attn2_sm100.cuh"
-#include "decoder_sm100.cuh"
 #include "decoder_stream_sm100.cuh"
 #include "gemm_sm100.cuh"
 #include "mel_host.h"
@@ -274,18 +273,12 @@ struct wt_engine {
   bool dec_persistent = false;
   int dec_cluster = 0, dec_group = 0, dec_groups_cap = 0, dec_active_clusters = 0;
   int dec_group_user = 0;  // wt_set_decoder_group (0 = automatic)
-  int attn_mode = -1;      // encoder attention kernel: -1 = not chosen yet, 0 = two CTAs per SM, 1 = one (WT_ATTN=1cta)
+  unsigned long long* d_hash = nullptr;   // wt_debug_hash accumulator
   int* gemm_sched = nullptr;  // {next tile, CTAs done} of the GEMM kernel's dynamic tile scheduler (self-resetting)
-  wt::DecLayerDev* d_dec_layers = nullptr;
-  float *pd_x = nullptr, *pd_qs = nullptr, *pd_att = nullptr, *pd_qx = nullptr, *pd_xpart = nullptr;
-  bf16* pd_hmid = nullptr;
-  unsigned* pd_xtickets = nullptr;
-  unsigned long long* pd_amax = nullptr;
+  float* pd_qs = nullptr;
   int* pd_finished = nullptr;
   unsigned long long* pd_trace = nullptr;  // WT_DEC_TRACE=1: per-phase ns of the persistent decoder (CTA 0)
-  int pd_xslots_cap = 0;
-  // streaming flavour (decoder_stream_sm100.cuh, the default): packed weight streams + one producer warp per CTA
-  bool dec_stream = false;
+  // decoder_stream_sm100.cuh: packed weight streams + one producer warp per CTA
   wt::DsLayerDev* d_ds_layers = nullptr;
   uint4* ds_w_logits = nullptr;
   float* ds_b_logits = nullptr;
@@ -354,6 +347,7 @@ struct wt_engine {
   bool f32mode() const { return precision == WT_PRECISION_FP32_VERIFY; }
 
   int init_frontend();
+  int init_kernels();
   int load_model(const char* path);
   int set_filters(const float* f, int n_mel_, int n_freq);
   int log_mel(const float* pcm, int n_clips, int n_samples, int pcm_mem, float* out, int out_mem, bool finalize);
@@ -372,6 +366,7 @@ struct wt_engine {
   int linear(const void* A, int M, const Lin& L, void* C, int flags, const void* addend = nullptr,
              unsigned long long* amax = nullptr);
   int layernorm(const void* in, const LNp& ln, void* out, int rows);
+  int attention_bf16(const void* qkv_, void* out, int n_clips, int S, int H);
   int get_map(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides,
               const uint32_t* box);
 };
@@ -393,17 +388,10 @@ int wt_engine::get_map(CUtensorMap* out, const void* base, int rank, const uint6
 template <int BN>
 static int launch_gemm_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMap& mw, wt::GemmBf16Params& p) {
   using S = wt::GemmSmem<BN>;
-  static bool attr_set[64] = {};
-  if (!attr_set[e->device & 63]) {
-    WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
-    attr_set[e->device & 63] = true;
-  }
   p.n_tiles_n = (p.N + BN - 1) / BN;
   const int n_tiles = p.tiles_per_batch * p.n_batches * p.n_tiles_n;
   const int grid = n_tiles < e->num_sms ? n_tiles : e->num_sms;
-  if (!e->gemm_sched) {
-    if (e->alloc(&e->gemm_sched, 2, true) != WT_OK) return WT_ERR_CUDA;
-  }
+  if (!e->gemm_sched) return fail(WT_ERR_STATE, "GEMM tile scheduler not allocated (engine not initialised)");
   p.sched = e->gemm_sched;
   e->pre_launch();
   wt::gemm_bf16_sm100_kernel<BN><<<grid, wt::kGemmThreads, S::kTotal, e->stream>>>(ma, mw, p);
@@ -503,6 +491,20 @@ int wt_engine::linear(const void* A, int M, const Lin& L, void* C, int flags, co
                    plain, amax);
 }
 
+// softmax(Q K^T / 8) V per (clip, head) on qkv [n_clips][S][3*H*64] bf16 -> out [n_clips][S][H*64] bf16
+int wt_engine::attention_bf16(const void* qkv_, void* out, int n_clips, int S, int H) {
+  const int d = H * 64;
+  CUtensorMap mq;
+  const uint64_t qd[3] = {(uint64_t)3 * d, (uint64_t)S, (uint64_t)n_clips};
+  const uint64_t qs[2] = {(uint64_t)3 * d * 2, (uint64_t)S * 3 * d * 2};
+  const uint32_t qbox[3] = {64, 128, 1};
+  WT_TRY(get_map(&mq, qkv_, 3, qd, qs, qbox));
+  stage = ST_ENC_ATTN;
+  pre_launch();
+  wt::attention2_sm100_kernel<<<dim3((S + 127) / 128, H, n_clips), wt::kAt2Threads, wt::Attn2Smem::kTotal, stream>>>(mq, (bf16*)out, S, H);
+  return check_launch("attention2_sm100_kernel");
+}
+
 int wt_engine::layernorm(const void* in, const LNp& ln, void* out, int rows) {
   const int D = dims.d_model;
   stage = decoding ? ST_DEC_LN : ST_ENC_LN;
@@ -534,6 +536,18 @@ int wt_engine::init_frontend() {
   WT_TRY(alloc(&d_mel, B * wt::kMaxMel * WT_N_FRAMES));
   WT_TRY(alloc(&d_clip_max, B));
   WT_CUDA_OK(cudaFuncSetAttribute(wt::mel_frames_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::kMelSmemBytes));
+  return init_kernels();
+}
+
+// Per-device kernel attributes and the GEMM tile scheduler's counters: set at engine creation (every engine sets them
+// again: the call is idempotent and thread-safe, unlike a process-wide "already set" flag), never on the hot path.
+int wt_engine::init_kernels() {
+  WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<64>::kTotal));
+  WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<128>::kTotal));
+  WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<192>::kTotal));
+  WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<256>::kTotal));
+  WT_CUDA_OK(cudaFuncSetAttribute(wt::attention2_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::Attn2Smem::kTotal));
+  WT_TRY(alloc(&gemm_sched, 2, true));   // cudaMemset here; wt_engine_create synchronises the device before returning
   return WT_OK;
 }
 
@@ -762,14 +776,8 @@ bool wt_engine::persistent_decoder_wanted() const {
 
 int wt_engine::init_persistent_decoder() {
   if (!persistent_decoder_wanted()) return WT_OK;
+  const void* kfn = (const void*)wt::decoder_stream_kernel;
   {
-    const char* ov = getenv("WT_DECODER");
-    dec_stream = !(ov && strcmp(ov, "cluster") == 0);
-  }
-  const void* kfn = dec_stream ? (const void*)wt::decoder_stream_kernel : (const void*)wt::decoder_persistent_kernel;
-  const int kthreads = dec_stream ? wt::kDsThreads : wt::kDecThreads;
-  int ksmem = wt::DecSmem::kTotal;
-  if (dec_stream) {
     const int kbK = dims.d_model / 32;
     if (dims.d_model % 64 != 0) return fail(WT_ERR_INVALID, "streaming decoder needs d_model %% 64 == 0");
     const int cand[6] = {8, 6, 4, 3, 2, 1};
@@ -781,11 +789,11 @@ int wt_engine::init_persistent_decoder() {
     if (ds_stages > wt::kDsMaxStages) ds_stages = wt::kDsMaxStages;
     if (const char* os = getenv("WT_DEC_STAGES")) ds_stages = atoi(os) < ds_stages ? atoi(os) : ds_stages;
     if (ds_stages < 2) return fail(WT_ERR_INVALID, "streaming decoder: shared memory holds only %d ring stages at d_model %d", ds_stages, dims.d_model);
-    ksmem = ds_smem = wt::DsSmem::total(dims.d_model, ds_stages);
+    ds_smem = wt::DsSmem::total(dims.d_model, ds_stages);
   }
-  WT_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, ksmem));
-  // cluster shape: 16 CTAs x 8 clips (8 clusters fill 128 SMs at B = 64) when the device can co-schedule a 16-CTA
-  // cluster per GPC, else the portable 8 CTAs x 4 clips. WT_DEC_CLUSTER / WT_DEC_GROUP override (probing).
+  WT_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, ds_smem));
+  // cluster shape: 16 CTAs when the device can co-schedule a 16-CTA cluster per GPC, else the portable 8.
+  // WT_DEC_CLUSTER / WT_DEC_GROUP override (probing).
   dec_cluster = 0;
   const int want[2] = {16, 8};
   const char* ocl = getenv("WT_DEC_CLUSTER");
@@ -801,8 +809,8 @@ int wt_engine::init_persistent_decoder() {
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(cs);
-    cfg.blockDim = dim3(kthreads);
-    cfg.dynamicSmemBytes = ksmem;
+    cfg.blockDim = dim3(wt::kDsThreads);
+    cfg.dynamicSmemBytes = ds_smem;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
@@ -813,50 +821,23 @@ int wt_engine::init_persistent_decoder() {
     if (n_active >= 1) { dec_cluster = cs; dec_active_clusters = n_active; }
     if (ocl) break;
   }
-  if (!dec_cluster) return fail(WT_ERR_CUDA, "decoder_persistent_kernel: no schedulable cluster shape");
+  if (!dec_cluster) return fail(WT_ERR_CUDA, "decoder_stream_kernel: no schedulable cluster shape");
   dec_group = dec_cluster >= 16 ? 8 : 4;
   if (const char* og = getenv("WT_DEC_GROUP")) dec_group = atoi(og);
   if (dec_group < 1 || dec_group > wt::kDecGroupMax) return fail(WT_ERR_INVALID, "WT_DEC_GROUP must be in [1, %d]", wt::kDecGroupMax);
-  const int d = dims.d_model, H = dims.n_heads, S = dims.n_audio_ctx;
-  std::vector<wt::DecLayerDev> hl(dims.n_dec_layers);
-  for (int i = 0; i < dims.n_dec_layers; ++i) {
-    DecLayer& L = dec[i];
-    wt::DecLayerDev& o = hl[i];
-    o.ln1_g = L.ln1.g; o.ln1_b = L.ln1.b; o.lnx_g = L.lnx.g; o.lnx_b = L.lnx.b; o.ln2_g = L.ln2.g; o.ln2_b = L.ln2.b;
-    o.w_qkv = (const bf16*)L.qkv.w; o.b_qkv = L.qkv.b;
-    o.w_out = (const bf16*)L.out.w; o.b_out = L.out.b;
-    o.w_xq = (const bf16*)L.xq.w; o.b_xq = L.xq.b;
-    o.w_xout = (const bf16*)L.xout.w; o.b_xout = L.xout.b;
-    o.w_fc1 = (const bf16*)L.fc1.w; o.b_fc1 = L.fc1.b;
-    o.w_fc2 = (const bf16*)L.fc2.w; o.b_fc2 = L.fc2.b;
-    o.kvx = (const bf16*)L.kvx;
-    o.kc = (bf16*)L.kc; o.vc = (bf16*)L.vc;
-  }
-  WT_TRY(alloc(&d_dec_layers, hl.size()));
-  WT_CUDA_OK(cudaMemcpy(d_dec_layers, hl.data(), hl.size() * sizeof(wt::DecLayerDev), cudaMemcpyHostToDevice));
+  const int d = dims.d_model;
   dec_groups_cap = (max_batch + dec_group - 1) / dec_group;
   const size_t R = (size_t)dec_groups_cap * wt::kDecGroupMax;  // scratch rows: kDecGroupMax per group
-  WT_TRY(alloc(&pd_x, R * d));
   WT_TRY(alloc(&pd_qs, R * d));
-  WT_TRY(alloc(&pd_att, R * d));
-  WT_TRY(alloc(&pd_qx, R * d));
-  WT_TRY(alloc(&pd_hmid, R * 4 * d));
-  // worst case slots per (clip, head): a group holding one clip -> per = ceil(H*cpp/cluster) chunks per CTA
-  const int cpp = (S + wt::kXaChunk - 1) / wt::kXaChunk;
-  const int per_min = (H * cpp + dec_cluster - 1) / dec_cluster;
-  pd_xslots_cap = (cpp + per_min - 1) / per_min + 1;
-  WT_TRY(alloc(&pd_xpart, R * H * (size_t)pd_xslots_cap * 66));
-  WT_TRY(alloc(&pd_xtickets, R * H, true));
-  WT_TRY(alloc(&pd_amax, R * (size_t)wt::kDecMaxCluster));
   WT_TRY(alloc(&pd_finished, (size_t)dec_groups_cap, true));
   if (const char* tr = getenv("WT_DEC_TRACE")) {
     if (tr[0] == '1') {
       WT_TRY(alloc(&pd_trace, 32, true));
-      fprintf(stderr, "[whisper_b200] persistent decoder (%s): cluster %d CTAs x %d clips, %d clusters co-resident, smem %d B, ring %d stages, upw %d\n",
-              dec_stream ? "stream" : "cluster", dec_cluster, dec_group, dec_active_clusters, ksmem, ds_stages, ds_upw);
+      fprintf(stderr, "[whisper_b200] streaming decoder: cluster %d CTAs x %d clips, %d clusters co-resident, smem %d B, ring %d stages, upw %d\n",
+              dec_cluster, dec_group, dec_active_clusters, ds_smem, ds_stages, ds_upw);
     }
   }
-  if (dec_stream) WT_TRY(init_stream_weights());
+  WT_TRY(init_stream_weights());
   dec_persistent = true;
   return WT_OK;
 }
@@ -923,7 +904,7 @@ int wt_engine::decode_persistent(int n_clips, int prompt_len, int max_total, int
   if (n_groups > dec_groups_cap)
     return fail(WT_ERR_INVALID, "decoder: %d clip groups of %d exceed the %d the scratch buffers were sized for", n_groups, gsz, dec_groups_cap);
   WT_CUDA_OK(cudaMemsetAsync(pd_finished, 0, (size_t)dec_groups_cap * sizeof(int), stream));
-  if (dec_stream) {
+  {
     wt::DsParams q{};
     q.layers = d_ds_layers;
     q.n_layers = dims.n_dec_layers;
@@ -965,55 +946,6 @@ int wt_engine::decode_persistent(int n_clips, int prompt_len, int max_total, int
     WT_CUDA_OK(cudaLaunchKernelEx(&cfg, wt::decoder_stream_kernel, q));
     return check_launch("decoder_stream_kernel");
   }
-  WT_CUDA_OK(cudaMemsetAsync(pd_xtickets, 0, (size_t)dec_groups_cap * wt::kDecGroupMax * H * sizeof(unsigned), stream));
-  wt::DecParams p{};
-  p.layers = d_dec_layers;
-  p.n_layers = dims.n_dec_layers;
-  p.n_clips = n_clips;
-  p.clip0 = 0;
-  p.group_clips = gsz;
-  if (const char* dbg = getenv("WT_DEC_DEBUG")) p.debug = atoi(dbg);
-  p.d = d; p.H = H; p.S = S; p.V = dims.n_vocab;
-  p.tok_emb = (const bf16*)tok_emb;
-  p.pos_emb = (const bf16*)dec_pos;
-  p.lnf_g = dec_ln.g; p.lnf_b = dec_ln.b;
-  p.tokens = tokens; p.lens = lens; p.done = done;
-  p.prompt_len = prompt_len; p.max_total = max_total; p.eot = eot;
-  p.x = pd_x; p.qs = pd_qs; p.att = pd_att; p.qx = pd_qx; p.hmid = pd_hmid;
-  p.xpart = pd_xpart; p.xtickets = pd_xtickets;
-  {
-    // slots per (clip, head) pair: the fullest and the last (smallest) group bound the range
-    int slots = 0;
-    const int last = n_clips - (n_groups - 1) * gsz;
-    const int cand[2] = {n_groups > 1 ? gsz : last, last};
-    const int cpp = (S + wt::kXaChunk - 1) / wt::kXaChunk;
-    for (int i = 0; i < 2; ++i) {
-      const int per = (cand[i] * H * cpp + dec_cluster - 1) / dec_cluster;
-      const int sl = (cpp + per - 1) / per + 1;
-      if (sl > slots) slots = sl;
-    }
-    p.xslots = slots;
-  }
-  if (p.xslots > pd_xslots_cap) return fail(WT_ERR_STATE, "cross-attention partial slots %d exceed capacity %d", p.xslots, pd_xslots_cap);
-  p.amax_part = pd_amax;
-  p.step_logits = keep_logits ? step_logits : nullptr;
-  p.step_logits_stride = (long long)max_batch * dims.n_vocab;
-  p.finished = pd_finished;
-  p.trace = pd_trace;
-  cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(n_groups * dec_cluster);
-  cfg.blockDim = dim3(wt::kDecThreads);
-  cfg.dynamicSmemBytes = wt::DecSmem::kTotal;
-  cfg.stream = stream;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeClusterDimension;
-  at[0].val.clusterDim.x = dec_cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-  cfg.attrs = at;
-  cfg.numAttrs = 1;
-  stage = ST_DEC_PERSISTENT;
-  pre_launch();
-  WT_CUDA_OK(cudaLaunchKernelEx(&cfg, wt::decoder_persistent_kernel, p));
-  return check_launch("decoder_persistent_kernel");
 }
 
 // mel -> encoder states (+ cross-attention K/V of every decoder layer), all resident.
@@ -1113,30 +1045,7 @@ int wt_engine::encode(const float* mel, int n_clips, int mel_mem, float* states_
       wt::attention_simt_kernel<float><<<dim3((S + 127) / 128, H, n_clips), 128, 0, stream>>>((const float*)qkv, (float*)att, S, H);
       WT_TRY(check_launch("attention_simt_kernel"));
     } else {
-      CUtensorMap mq;
-      const uint64_t qd[3] = {(uint64_t)3 * d, (uint64_t)S, (uint64_t)n_clips};
-      const uint64_t qs[2] = {(uint64_t)3 * d * 2, (uint64_t)S * 3 * d * 2};
-      const uint32_t qbox[3] = {64, 128, 1};
-      WT_TRY(get_map(&mq, qkv, 3, qd, qs, qbox));
-      static bool attn_attr[64] = {};
-      if (!attn_attr[device & 63]) {
-        WT_CUDA_OK(cudaFuncSetAttribute(wt::attention_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::AttnSmem::kTotal));
-        WT_CUDA_OK(cudaFuncSetAttribute(wt::attention2_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::Attn2Smem::kTotal));
-        attn_attr[device & 63] = true;
-      }
-      if (attn_mode < 0) {  // WT_ATTN=1cta at engine creation time selects the one-CTA-per-SM kernel (attn_sm100.cuh)
-        const char* v = getenv("WT_ATTN");
-        attn_mode = (v && strcmp(v, "1cta") == 0) ? 1 : 0;
-      }
-      const bool one_cta = attn_mode == 1;
-      pre_launch();
-      if (one_cta) {
-        wt::attention_sm100_kernel<<<dim3((S + 127) / 128, H, n_clips), wt::kAtThreads, wt::AttnSmem::kTotal, stream>>>(mq, (bf16*)att, S, H);
-        WT_TRY(check_launch("attention_sm100_kernel"));
-      } else {  // two CTAs per SM (attn2_sm100.cuh)
-        wt::attention2_sm100_kernel<<<dim3((S + 127) / 128, H, n_clips), wt::kAt2Threads, wt::Attn2Smem::kTotal, stream>>>(mq, (bf16*)att, S, H);
-        WT_TRY(check_launch("attention2_sm100_kernel"));
-      }
+      WT_TRY(attention_bf16(qkv, att, n_clips, S, H));
     }
     WT_TRY(linear(att, M2, L.out, x, 0, x));
     WT_TRY(layernorm(x, L.ln2, xn, M2));
@@ -1458,6 +1367,48 @@ int wt_debug_decoder_trace(wt_engine* e, uint64_t* out32, int reset) {
   return WT_OK;
 }
 
+// Debug: digest of a resident buffer as the last call left it (the bitwise-reproducibility tests and the stage bisect).
+int wt_debug_hash(wt_engine* e, const char* what, int n_clips, uint64_t* out) {
+  if (!e || !what || !out) return fail(WT_ERR_INVALID, "null argument");
+  if (n_clips < 1 || n_clips > e->max_batch) return fail(WT_ERR_INVALID, "n_clips %d outside [1, max_batch=%d]", n_clips, e->max_batch);
+  cudaSetDevice(e->device);
+  const std::string w(what);
+  const size_t B = (size_t)n_clips;
+  const void* buf = nullptr;
+  size_t bytes = 0;
+  if (w == "mel_raw") { buf = e->d_mel_raw; bytes = B * e->n_mel * WT_N_FRAMES * 4; }
+  else if (!e->has_model) return fail(WT_ERR_STATE, "engine was created without weights");
+  else {
+    const size_t d = e->dims.d_model, S = e->dims.n_audio_ctx, H = e->dims.n_heads, esz = e->esz;
+    if (w == "mel_tm") { buf = e->mel_tm; bytes = B * (WT_N_FRAMES + 2) * e->dims.n_mels * esz; }
+    else if (w == "conv1") { buf = e->x1; bytes = B * (WT_N_FRAMES + 2) * d * esz; }
+    else if (w == "x") { buf = e->x; bytes = B * S * d * esz; }
+    else if (w == "qkv") { buf = e->qkv; bytes = B * S * 3 * d * esz; }
+    else if (w == "att") { buf = e->att; bytes = B * S * d * esz; }
+    else if (w == "hidden") { buf = e->hbuf; bytes = B * S * 4 * d * esz; }
+    else if (w == "enc_out") { buf = e->enc_out; bytes = B * S * d * esz; }
+    else if (w == "tokens") { buf = e->tokens; bytes = B * 32 * 4; }
+    else if (w.rfind("cross_kv", 0) == 0) {
+      const int l = atoi(w.c_str() + 8);
+      if (l < 0 || l >= (int)e->dec.size()) return fail(WT_ERR_INVALID, "no decoder layer %d", l);
+      if (e->dec[l].kvx) {
+        const size_t cpp = (S + wt::kXaChunk - 1) / wt::kXaChunk;
+        buf = e->dec[l].kvx; bytes = B * H * cpp * 2 * wt::kXaChunk * 64 * esz;
+      } else { buf = e->dec[l].kx; bytes = B * H * S * 64 * esz; }
+    } else return fail(WT_ERR_INVALID, "unknown buffer '%s'", what);
+  }
+  if (!buf) return fail(WT_ERR_STATE, "buffer '%s' is not allocated in this engine", what);
+  if (!e->d_hash) WT_TRY(e->alloc(&e->d_hash, 1));
+  WT_CUDA_OK(cudaMemsetAsync(e->d_hash, 0, 8, e->stream));
+  wt::hash_words_kernel<<<e->num_sms * 8, 256, 0, e->stream>>>((const uint32_t*)buf, (long long)(bytes / 4), e->d_hash);
+  WT_CUDA_OK(cudaGetLastError());
+  unsigned long long h = 0;
+  WT_CUDA_OK(cudaMemcpyAsync(&h, e->d_hash, 8, cudaMemcpyDeviceToHost, e->stream));
+  WT_CUDA_OK(cudaStreamSynchronize(e->stream));
+  *out = h;
+  return WT_OK;
+}
+
 int wt_profile_enable(wt_engine* e, int enable) {
   if (!e) return fail(WT_ERR_INVALID, "engine is null");
   cudaSetDevice(e->device);
@@ -1485,9 +1436,7 @@ int wt_profile_read(wt_engine* e, float* ms_out, int32_t* launches_out, int n_st
 int wt_stage_count(void) { return ST_COUNT; }
 const char* wt_stage_name(int i) { return (i >= 0 && i < ST_COUNT) ? kStageNames[i] : ""; }
 
-int wt_debug_gemm_bf16(void* cuda_stream, const void* A, const void* W, const float* bias, void* C, int M, int N, int K,
-                       int flags) {
-  if (!A || !W || !C || M < 1 || N < 8 || K < 8 || (K % 8) || (N % 8)) return fail(WT_ERR_INVALID, "bad GEMM arguments");
+static int debug_scratch_engine(void* cuda_stream, wt_engine** out) {
   static thread_local wt_engine* scratch = nullptr;
   int dev = 0;
   WT_CUDA_OK(cudaGetDevice(&dev));
@@ -1498,15 +1447,57 @@ int wt_debug_gemm_bf16(void* cuda_stream, const void* A, const void* W, const fl
     scratch = new wt_engine();
     scratch->device = dev;
     scratch->num_sms = prop.multiProcessorCount;
+    WT_TRY(scratch->init_kernels());
+    WT_CUDA_OK(cudaDeviceSynchronize());   // the scheduler counters' memset precedes the first launch on any stream
   }
   scratch->stream = (cudaStream_t)cuda_stream;
   scratch->precision = WT_PRECISION_BF16;
+  *out = scratch;
+  return WT_OK;
+}
+
+int wt_debug_gemm_bf16(void* cuda_stream, const void* A, const void* W, const float* bias, void* C, int M, int N, int K,
+                       int flags) {
+  if (!A || !W || !C || M < 1 || N < 8 || K < 8 || (K % 8) || (N % 8)) return fail(WT_ERR_INVALID, "bad GEMM arguments");
+  wt_engine* scratch = nullptr;
+  WT_TRY(debug_scratch_engine(cuda_stream, &scratch));
   Lin L;
   L.w = const_cast<void*>(W);
   L.b = const_cast<float*>(bias);
   L.N = N;
   L.K = K;
   return scratch->linear(A, M, L, C, flags & wt::EPI_GELU);
+}
+
+int wt_debug_gemm_ex(void* cuda_stream, const wt_debug_gemm_args* a) {
+  if (!a || a->struct_size != (int32_t)sizeof(wt_debug_gemm_args)) return fail(WT_ERR_INVALID, "wt_debug_gemm_args.struct_size mismatch");
+  if (!a->A || !a->W || a->N < 8 || (a->N % 8) || a->K_total < 8 || a->taps < 1 || a->taps > 3 || a->rows_per_batch < 1 || a->n_batches < 1)
+    return fail(WT_ERR_INVALID, "bad GEMM arguments");
+  wt_engine* scratch = nullptr;
+  WT_TRY(debug_scratch_engine(cuda_stream, &scratch));
+  Lin L;
+  L.w = const_cast<void*>(a->W);
+  L.b = (a->flags & wt::EPI_BIAS) ? const_cast<float*>(a->bias) : nullptr;
+  L.N = a->N;
+  L.K = a->K_total;
+  scratch->next_kv_k = a->kv_out;
+  scratch->next_kv_v = a->kv_out_v;
+  scratch->next_kv_chunked = a->kv_chunked != 0;
+  scratch->dims.n_audio_ctx = a->kv_S;
+  scratch->dims.n_heads = a->kv_H;
+  scratch->stage = ST_ENC_GEMM;
+  const RowMap cmap{a->c_batch_stride, a->c_rows > 0 ? a->c_rows : 1, a->c_row_stride};
+  const RowMap amap{a->add_batch_stride, a->add_rows > 0 ? a->add_rows : 1, a->add_row_stride};
+  return scratch->gemm_bf16(a->A, a->a_dims, a->a_strides, a->rows_per_batch, a->n_batches, L, a->K_total, a->taps, a->tap_k,
+                            a->tap_c0, a->tap_row, a->C, cmap, a->flags & ~wt::EPI_BIAS, a->addend, amap,
+                            (unsigned long long*)a->argmax_part, a->force_bn);
+}
+
+int wt_debug_attention_bf16(void* cuda_stream, const void* qkv, void* out, int n_clips, int S, int H) {
+  if (!qkv || !out || n_clips < 1 || S < 1 || H < 1) return fail(WT_ERR_INVALID, "bad attention arguments");
+  wt_engine* scratch = nullptr;
+  WT_TRY(debug_scratch_engine(cuda_stream, &scratch));
+  return scratch->attention_bf16(qkv, out, n_clips, S, H);
 }
 
 }  // extern "C"

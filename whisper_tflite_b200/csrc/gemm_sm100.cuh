@@ -204,7 +204,11 @@ struct GemmSmem {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kScratchRowBytes = 128 + 16;  // 64 bf16 or 32 f32 per row + pad (keeps 16B phases conflict-free)
   static constexpr int kScratchBytes = kGemmEpiGroups * 4 * 32 * kScratchRowBytes;
-  static constexpr int kBiasBytes = 2 * BN * 4;
+  // bias staging: per epilogue group TWO buffers, alternating with the group's tiles. A warp that has finished tile i
+  // writes tile i+2's bias (other n0) while a slower warp of the group may still be reading tile i's: with one buffer
+  // that was a write-after-read race (the run-to-run token differences of round 1); with two, the writer of tile i+4's
+  // bias has passed tile i+2's group barrier, which every warp reaches only after its last read of tile i's buffer.
+  static constexpr int kBiasBytes = 4 * BN * 4;
   static constexpr int kTileQ = 4;      // tile-index queue producer -> MMA issuer + epilogue group (even: it & 1 keeps its group)
   static constexpr int kBarBytes = (2 * kStages + 4 + 2 * kTileQ) * 8 + 16 + kTileQ * 4;
   static constexpr int kTotal = kStages * kStageBytes + kScratchBytes + kBiasBytes + kBarBytes + 1024;
@@ -353,7 +357,7 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
       const int tn = tile % p.n_tiles_n, tm = tile / p.n_tiles_n;
       const int batch = tm / p.tiles_per_batch, row0 = (tm % p.tiles_per_batch) * kGemmBM;
       const int n0 = tn * BN;
-      float* bias_s = s_bias + acc * BN;
+      float* bias_s = s_bias + (acc * 2 + ((it >> 1) & 1)) * BN;
       if (p.flags & EPI_BIAS)
         for (int i = et; i < BN; i += 128) bias_s[i] = (n0 + i < p.N) ? __ldg(p.bias + n0 + i) : 0.0f;
       asm volatile("bar.sync %0, 128;" ::"r"(1 + eg) : "memory");

@@ -497,7 +497,9 @@ __global__ void __launch_bounds__(256) split_heads_kv_kernel(const T* kv, T* kx,
 __device__ __forceinline__ unsigned long long pack_val_idx(float v, unsigned idx) {
   unsigned u = __float_as_uint(v);
   u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);  // monotone map float -> unsigned
-  if (v != v) u = 0u;                               // NaN loses
+  // NaN never satisfies `*p >= max_value` (whisper.cpp:353), so it loses everywhere — except at index 0, where it IS the
+  // initial max_value (:348) and no later element can replace it
+  if (v != v) u = idx == 0u ? 0xffffffffu : 0u;
   return ((unsigned long long)u << 32) | idx;
 }
 __device__ __forceinline__ unsigned long long u64_max(unsigned long long a, unsigned long long b) { return a > b ? a : b; }
@@ -660,6 +662,23 @@ template <class TI, class TO>
 __global__ void __launch_bounds__(256) convert_kernel(const TI* in, TO* out, long long n) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     out[i] = from_f32<TO>(to_f32<TI>(in[i]));
+}
+
+// Debug: order-independent 64-bit digest of a buffer of 32-bit words: sum over words of mix(index, word). Two runs that
+// left the same bytes in the buffer give the same digest whatever the launch geometry (wt_debug_hash).
+__device__ __forceinline__ unsigned long long hash_mix64(unsigned long long z) {
+  z += 0x9e3779b97f4a7c15ull;
+  z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+  z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+  return z ^ (z >> 31);
+}
+__global__ void __launch_bounds__(256) hash_words_kernel(const uint32_t* __restrict__ w, long long n, unsigned long long* out) {
+  unsigned long long acc = 0ull;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    acc += hash_mix64(((unsigned long long)i << 32) ^ (unsigned long long)w[i]);
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0 && acc) atomicAdd(out, acc);
 }
 
 }  // namespace wt
