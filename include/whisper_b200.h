@@ -112,6 +112,16 @@ WT_API int wt_transcribe_tokens(wt_engine* e, const float* pcm, int n_clips, int
                                 const int64_t* prompt, int prompt_len, int max_total_tokens, int64_t eot,
                                 int32_t* ids_out, int32_t* lens_out, int out_mem);
 
+/* int16 PCM ingest: the same two calls on 16-bit samples as a WAV file holds them. The
+ * conversion the reference does on the host — static_cast<float>(s) / static_cast<float>(INT16_MAX), wav_util.cpp:70-73
+ * (wav_read_legacy) and :120-122 (wav_read, mono) — happens in the mel kernel's staging load, so the mel is bit-equal to
+ * wt_log_mel on the converted samples and a host batch costs 0.96 MB per clip on PCIe instead of 1.92 MB. */
+WT_API int wt_log_mel_i16(wt_engine* e, const int16_t* pcm, int n_clips, int n_samples, int pcm_mem, float* mel_out,
+                          int out_mem);
+WT_API int wt_transcribe_tokens_i16(wt_engine* e, const int16_t* pcm, int n_clips, int n_samples, int pcm_mem,
+                                    const int64_t* prompt, int prompt_len, int max_total_tokens, int64_t eot,
+                                    int32_t* ids_out, int32_t* lens_out, int out_mem);
+
 /* keep_logits engines only: f32 logits of decode step `step` (0 = first generated token), [n_clips][n_vocab]. */
 WT_API int wt_get_step_logits(wt_engine* e, int step, int n_clips, float* out, int out_mem);
 

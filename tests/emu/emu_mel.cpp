@@ -8,7 +8,7 @@ extern "C" int emu_log_mel(const float* pcm, int n_clips, int n_samples, const f
                            float* raw_out, float* mel_out) {
   using namespace wt;
   MelHostTables t = build_mel_tables(filters, n_mel);
-  MelParams p;
+  MelParams p{};
   const int n_len = n_samples / kHop;
   std::vector<int> cmax(n_clips, INT_MIN);
   p.pcm = pcm;

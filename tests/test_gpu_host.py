@@ -128,3 +128,46 @@ def test_encdec_cli_on_wav_file(host, assets, oracle_built, filters):
     blob_en = host.Blob(open(assets["vocab_en"], "rb").read(), False)
     expect = host.remove_extra_spaces(blob_en.decode(ids2).decode()).encode()
     assert expect in out2.stdout
+
+
+def test_language_task_and_special_token_options(host, assets, oracle_built, filters):
+    """what the reference hard-codes — language "de" (whisper.cpp:327), transcribe
+    (:336), omit_special_tokens = false (:733, :766) — as options whose defaults are the reference's. The prompt the
+    engine builds must be [sot, 50259 + language_id(code), transcribe | translate, notimestamps]: transcripts equal
+    decode(oracle greedy ids for that prompt) in the verification mode."""
+    pcm = synth.synth_pcm(1, seed=14)[0]
+    blob = host.Blob(open(assets["vocab_multi"], "rb").read(), True)
+    for etype in (host.ENGINE_ENCDEC, host.ENGINE_MONOLITH):
+        eng = host.HostEngine(etype, assets["prefix"], assets["vocab_multi"], True)
+        default_text, _ = eng.transcribe(pcm)
+        ids_de = oracle_ids(assets, pcm, oracle_built, filters, (50258, 50261, 50359, 50363), EOT)
+        assert default_text == blob.decode(ids_de)                        # defaults: "de", transcribe, specials kept
+        assert not eng.set_language("xx")                                 # unknown code: refused, nothing changes
+        assert eng.transcribe(pcm)[0] == default_text
+        assert eng.set_language("fr") and host.language_id("fr") == 6
+        ids_fr = oracle_ids(assets, pcm, oracle_built, filters, (50258, 50259 + 6, 50359, 50363), EOT)
+        text_fr, _ = eng.transcribe(pcm)
+        assert text_fr == blob.decode(ids_fr) and text_fr.startswith(b"<|startoftranscript_|><|lang-fr|><|transcribe|>")
+        eng.set_task(True)                                                # translate: token 50358 (unshifted, whisper.cpp:218-226)
+        ids_tr = oracle_ids(assets, pcm, oracle_built, filters, (50258, 50259 + 6, 50358, 50363), EOT)
+        assert eng.transcribe(pcm)[0] == blob.decode(ids_tr)
+        eng.set_omit_special_tokens(True)                                 # decode keeps only ids < token_eot (whisper.cpp:641-650)
+        assert eng.transcribe(pcm)[0] == blob.decode(ids_tr, True)
+        assert b"<|" not in blob.decode(ids_tr, True)
+        eng.close()
+
+
+def test_int16_ingest_matches_host_conversion(host, assets):
+    """16-bit samples go to the device as they are; the `/ INT16_MAX` of wav_read_legacy /
+    wav_read (wav_util.cpp:70-73, :120-122) happens in the mel kernel's staging load. Transcripts must equal those of
+    the f32 call on host-converted samples (bit-equal mel => identical ids), for both engine kinds, through a
+    max_batch = 2 engine that has to chunk 3 clips."""
+    pcm16 = np.clip(synth.synth_pcm(3, seed=15) * 25000.0, -32768, 32767).astype(np.int16)
+    pcm16[1, 300000:] = 0
+    as_f32 = (pcm16.astype(np.float32) / np.float32(32767.0)).astype(np.float32)
+    for etype in (host.ENGINE_ENCDEC, host.ENGINE_MONOLITH):
+        eng = host.HostEngine(etype, assets["prefix"], assets["vocab_multi"], True)
+        assert eng.transcribe_batch_i16(pcm16) == eng.transcribe_batch(as_f32)
+        # short clips are zero-padded to 30 s like the f32 path (whisper.cpp:753)
+        assert eng.transcribe_batch_i16(pcm16[:1, :200000])[0] == eng.transcribe_batch(as_f32[:1, :200000])[0]
+        eng.close()

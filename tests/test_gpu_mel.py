@@ -95,3 +95,24 @@ def test_mel_errors(eng):
         eng.log_mel(np.zeros((65, 480000), np.float32))  # > max_batch
     with pytest.raises(capi.WhisperB200Error):
         eng.log_mel(np.zeros((1, 100), np.float32))  # < one hop
+
+
+def test_int16_pcm_is_bit_equal_to_f32_path(filters):
+    """wt_log_mel_i16: the staging load converts static_cast<float>(s) / static_cast<float>(INT16_MAX) (wav_util.cpp:70-73);
+    the mel must be BIT-equal to wt_log_mel on the host-converted samples — full windows, a ragged length that is not
+    a multiple of 8 (scalar staging path), host and device buffers."""
+    import torch
+    from whisper_tflite_b200 import capi
+    rs = np.random.RandomState(8)
+    eng = capi.Engine(None, max_batch=3, filters=filters)
+    for n in (480000, 160 * 37 + 3):
+        p16 = rs.randint(-32768, 32768, size=(3, n)).astype(np.int16)
+        p16[1, n // 2:] = 0
+        f32 = (p16.astype(np.float32) / np.float32(32767.0)).astype(np.float32)
+        a = eng.log_mel(p16)
+        b = eng.log_mel(f32)
+        assert a.shape == b.shape == (3, 80, n // 160)
+        np.testing.assert_array_equal(a.view(np.uint32), b.view(np.uint32))
+        c = eng.log_mel(torch.from_numpy(p16).cuda())
+        np.testing.assert_array_equal(c.view(np.uint32), b.view(np.uint32))
+    eng.close()

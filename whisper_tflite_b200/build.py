@@ -45,6 +45,16 @@ def build_cuda(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+def build_cuda_variant(suffix: str, extra_flags) -> str:
+    """A second in-tree library from the same sources with extra nvcc flags (profiling variants: -DDS_TRACE_FINE=1,
+    -DDS_PROBE); selected at run time with WT_LIB=<path>."""
+    out = os.path.join(CSRC, f"libwhisper_b200_{suffix}.so")
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h"))]
+    if _newer(out, deps):
+        subprocess.check_call([_nvcc()] + NVCC_FLAGS + list(extra_flags) + ["-o", out, os.path.join(CSRC, "engine.cu"), "-lcudart"])
+    return out
+
+
 def build_host(force: bool = False) -> str:
     if not os.path.isdir(HOST):
         return ""

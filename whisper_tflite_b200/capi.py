@@ -15,7 +15,8 @@ import numpy as np
 from . import synth
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "csrc", "libwhisper_b200.so")
+# WT_LIB selects another in-tree build of the same sources (e.g. the -DDS_TRACE_FINE=1 variant tools/dec_trace.py builds)
+LIB_PATH = os.environ.get("WT_LIB") or os.path.join(HERE, "csrc", "libwhisper_b200.so")
 
 WT_HOST, WT_DEVICE = 0, 1
 PRECISION_BF16, PRECISION_FP32_VERIFY = 0, 1
@@ -28,7 +29,8 @@ EXPORTED = [
     "wt_synchronize", "wt_log_mel", "wt_encode", "wt_decode_greedy", "wt_transcribe_tokens",
     "wt_get_step_logits", "wt_launch_count", "wt_last_error", "wt_version", "wt_debug_gemm_bf16",
     "wt_profile_enable", "wt_profile_read", "wt_stage_count", "wt_stage_name", "wt_debug_decoder_trace",
-    "wt_set_decoder_group", "wt_debug_hash", "wt_debug_gemm_ex", "wt_debug_attention_bf16",
+    "wt_set_decoder_group", "wt_debug_hash", "wt_debug_gemm_ex", "wt_debug_attention_bf16", "wt_log_mel_i16",
+    "wt_transcribe_tokens_i16",
 ]
 
 
@@ -84,6 +86,10 @@ def _ptr_mem(a):
         assert a.is_contiguous()
         return a.data_ptr(), (WT_DEVICE if a.is_cuda else WT_HOST), a
     raise TypeError(type(a))
+
+
+def _is_i16(a) -> bool:
+    return str(getattr(a, "dtype", "")).replace("torch.", "") == "int16"
 
 
 class Engine:
@@ -143,7 +149,8 @@ class Engine:
         if out is None:
             out = np.empty((n_clips, 80, n_samples // 160), dtype=np.float32)
         o, omem, _k2 = _ptr_mem(out)
-        _check(self.lib.wt_log_mel(self.h, ctypes.c_void_p(p), n_clips, n_samples, mem, ctypes.c_void_p(o), omem))
+        fn = self.lib.wt_log_mel_i16 if _is_i16(pcm) else self.lib.wt_log_mel   # int16 samples: converted on the device
+        _check(fn(self.h, ctypes.c_void_p(p), n_clips, n_samples, mem, ctypes.c_void_p(o), omem))
         return out
 
     # ---- Encoder::forward ----
@@ -184,9 +191,9 @@ class Engine:
         i, imem, _k2 = _ptr_mem(ids_out)
         l, lmem, _k3 = _ptr_mem(lens_out)
         assert imem == lmem
-        _check(self.lib.wt_transcribe_tokens(self.h, ctypes.c_void_p(p), n_clips, n_samples, mem, pr, len(prompt),
-                                             max_total_tokens, ctypes.c_int64(eot), ctypes.c_void_p(i),
-                                             ctypes.c_void_p(l), imem))
+        fn = self.lib.wt_transcribe_tokens_i16 if _is_i16(pcm) else self.lib.wt_transcribe_tokens
+        _check(fn(self.h, ctypes.c_void_p(p), n_clips, n_samples, mem, pr, len(prompt), max_total_tokens,
+                  ctypes.c_int64(eot), ctypes.c_void_p(i), ctypes.c_void_p(l), imem))
         return ids_out, lens_out
 
     def profile(self, enable: bool):

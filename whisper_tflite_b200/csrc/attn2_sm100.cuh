@@ -276,8 +276,12 @@ attention2_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat
       float mx_blk;
       float l_blk = valid >= 128 ? at2_pass2<false, kAt2Prefetch2>(t_s, p_row_s, sw, c_scale, m_ref, valid, mx_blk)
                                  : at2_pass2<true, false>(t_s, p_row_s, sw, c_scale, m_ref, valid, mx_blk);
-      if (mx_blk * c_scale > m_ref + 64.0f) {
-        m_ref = mx_blk * c_scale;
+      // The redo is decided per WARP: tcgen05.ld is .sync.aligned, so all 32 lanes must take the branch together (a lane
+      // on its own — the round-1 code — is undefined behaviour and hung the kernel in tests/test_gpu_kernels.py's score
+      // jump case). Lanes whose row did not jump repeat the block with their unchanged reference: identical results.
+      const bool jump = mx_blk * c_scale > m_ref + 64.0f;
+      if (__any_sync(0xffffffffu, jump)) {
+        if (jump) m_ref = mx_blk * c_scale;
         l_blk = at2_pass2<true, false>(t_s, p_row_s, sw, c_scale, m_ref, valid, mx_blk);
       }
       const float alpha = ex2_approx(m_run - m_ref);   // previous reference -> this block's

@@ -350,7 +350,7 @@ struct wt_engine {
   int init_kernels();
   int load_model(const char* path);
   int set_filters(const float* f, int n_mel_, int n_freq);
-  int log_mel(const float* pcm, int n_clips, int n_samples, int pcm_mem, float* out, int out_mem, bool finalize);
+  int log_mel(const void* pcm, int n_clips, int n_samples, int pcm_mem, float* out, int out_mem, bool finalize, bool i16 = false);
   int encode(const float* mel, int n_clips, int mel_mem, float* states_out, int out_mem, bool from_raw);
   int decode(int n_clips, const int64_t* prompt, int prompt_len, int max_total, int64_t eot, int32_t* ids, int32_t* lens_o,
              int out_mem);
@@ -570,15 +570,15 @@ int wt_engine::set_filters(const float* f, int n_mel_, int n_freq) {
 }
 
 // pcm -> raw log10 mel + per-clip max (resident); optionally the reference-layout normalised f32 mel.
-int wt_engine::log_mel(const float* pcm, int n_clips, int n_samples, int pcm_mem, float* out, int out_mem,
-                       bool finalize) {
+int wt_engine::log_mel(const void* pcm, int n_clips, int n_samples, int pcm_mem, float* out, int out_mem,
+                       bool finalize, bool i16) {
   if (!filters_set) return fail(WT_ERR_STATE, "wt_set_mel_filters has not been called");
   if (n_clips < 1 || n_clips > max_batch) return fail(WT_ERR_INVALID, "n_clips %d outside [1, max_batch=%d]", n_clips, max_batch);
   if (n_samples < wt::kHop || n_samples > WT_N_SAMPLES) return fail(WT_ERR_INVALID, "n_samples %d outside [160, 480000]", n_samples);
   if (!pcm) return fail(WT_ERR_INVALID, "pcm is null");
-  const float* src = pcm;
-  if (pcm_mem == WT_HOST) {
-    WT_CUDA_OK(cudaMemcpyAsync(d_pcm, pcm, (size_t)n_clips * n_samples * 4, cudaMemcpyHostToDevice, stream));
+  const void* src = pcm;
+  if (pcm_mem == WT_HOST) {   // int16 samples take half the staging buffer (and half the PCIe traffic)
+    WT_CUDA_OK(cudaMemcpyAsync(d_pcm, pcm, (size_t)n_clips * n_samples * (i16 ? 2 : 4), cudaMemcpyHostToDevice, stream));
     src = d_pcm;
   }
   const int n_len = n_samples / wt::kHop;
@@ -587,7 +587,8 @@ int wt_engine::log_mel(const float* pcm, int n_clips, int n_samples, int pcm_mem
   wt::fill_int_kernel<<<(n_clips + 255) / 256, 256, 0, stream>>>(d_clip_max, INT_MIN, n_clips);
   WT_TRY(check_launch("fill_int_kernel"));
   wt::MelParams p{};
-  p.pcm = src;
+  p.pcm = i16 ? nullptr : (const float*)src;
+  p.pcm_i16 = i16 ? (const short*)src : nullptr;
   p.raw = d_mel_raw;
   p.clip_max = d_clip_max;
   p.hann = d_hann;
@@ -1332,6 +1333,23 @@ int wt_transcribe_tokens(wt_engine* e, const float* pcm, int n_clips, int n_samp
   cudaSetDevice(e->device);
   if (n_samples != WT_N_SAMPLES) return fail(WT_ERR_INVALID, "wt_transcribe_tokens needs 480000-sample windows (pad/trim like whisper.cpp:753)");
   WT_TRY(e->log_mel(pcm, n_clips, n_samples, pcm_mem == WT_HOST ? WT_HOST : WT_DEVICE, nullptr, WT_DEVICE, false));
+  WT_TRY(e->encode(nullptr, n_clips, WT_DEVICE, nullptr, WT_DEVICE, true));
+  return e->decode(n_clips, prompt, prompt_len, max_total_tokens, eot, ids_out, lens_out, out_mem);
+}
+
+int wt_log_mel_i16(wt_engine* e, const int16_t* pcm, int n_clips, int n_samples, int pcm_mem, float* mel_out, int out_mem) {
+  if (!e) return fail(WT_ERR_INVALID, "engine is null");
+  cudaSetDevice(e->device);
+  return e->log_mel(pcm, n_clips, n_samples, pcm_mem, mel_out, out_mem, true, true);
+}
+
+int wt_transcribe_tokens_i16(wt_engine* e, const int16_t* pcm, int n_clips, int n_samples, int pcm_mem, const int64_t* prompt,
+                             int prompt_len, int max_total_tokens, int64_t eot, int32_t* ids_out, int32_t* lens_out,
+                             int out_mem) {
+  if (!e) return fail(WT_ERR_INVALID, "engine is null");
+  cudaSetDevice(e->device);
+  if (n_samples != WT_N_SAMPLES) return fail(WT_ERR_INVALID, "wt_transcribe_tokens_i16 needs 480000-sample windows (pad/trim like whisper.cpp:753)");
+  WT_TRY(e->log_mel(pcm, n_clips, n_samples, pcm_mem == WT_HOST ? WT_HOST : WT_DEVICE, nullptr, WT_DEVICE, false, true));
   WT_TRY(e->encode(nullptr, n_clips, WT_DEVICE, nullptr, WT_DEVICE, true));
   return e->decode(n_clips, prompt, prompt_len, max_total_tokens, eot, ids_out, lens_out, out_mem);
 }

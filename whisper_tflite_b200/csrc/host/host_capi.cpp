@@ -142,3 +142,21 @@ WTH_API int wth_engine_transcribe_batch(void* e, const float* pcm, int n_clips, 
   }
   return off;
 }
+// ---- ADDED options / int16 ingest (whisper.h mirror: Engine::set_language / set_task / set_omit_special_tokens,
+//      transcribe_batch_i16) ----
+WTH_API int wth_engine_set_language(void* e, const char* code) { return static_cast<whisper::Engine*>(e)->set_language(code) ? 1 : 0; }
+WTH_API void wth_engine_set_task(void* e, int translate) { static_cast<whisper::Engine*>(e)->set_task(translate != 0); }
+WTH_API void wth_engine_set_omit_special_tokens(void* e, int omit) { static_cast<whisper::Engine*>(e)->set_omit_special_tokens(omit != 0); }
+WTH_API int wth_engine_transcribe_batch_i16(void* e, const int16_t* pcm, int n_clips, int n_samples, char* buf, int cap) {
+  std::vector<std::vector<int16_t>> clips(n_clips);
+  for (int i = 0; i < n_clips; ++i) clips[i].assign(pcm + static_cast<size_t>(i) * n_samples, pcm + static_cast<size_t>(i + 1) * n_samples);
+  const std::vector<std::string> text = static_cast<whisper::Engine*>(e)->transcribe_batch_i16(clips);
+  int off = 0;
+  for (const std::string& s : text) {
+    if (off + static_cast<int>(s.size()) + 1 > cap) return -2;
+    std::memcpy(buf + off, s.data(), s.size());
+    off += static_cast<int>(s.size());
+    buf[off++] = 0;
+  }
+  return off;
+}

@@ -150,9 +150,17 @@ std::vector<float> Encoder::states(const EncoderOut& out) {
 }
 
 std::vector<int64_t> Decoder::prompt() const {
-  // whisper.cpp:327: 50259 + language index; the tag is hard-coded to "de" in the reference and kept so.
-  const int64_t target_lang_id = 50259 + language_id("de");
-  return {vocab_.token_sot, target_lang_id, vocab_.token_transcribe, vocab_.token_not};
+  // whisper.cpp:327: 50259 + language index; the reference hard-codes "de" and transcribe, which stay the defaults
+  const int64_t target_lang_id = 50259 + language_id(options_.language);
+  return {vocab_.token_sot, target_lang_id, options_.translate ? vocab_.token_translate : vocab_.token_transcribe,
+          vocab_.token_not};
+}
+
+bool Engine::set_language(const std::string& code) {
+  if (language_id(code) >= static_cast<int>(language_meta.size())) return false;  // unknown code (whisper.cpp:510-515)
+  options_.language = code;
+  on_options();
+  return true;
 }
 
 std::vector<std::vector<int64_t>> Decoder::forward_batch(EncoderOut enc) {
@@ -331,6 +339,13 @@ const float* stage(std::vector<std::vector<float>>& clips, size_t first, size_t 
   for (size_t i = 0; i < n; ++i) std::memcpy(staging.data() + i * kWindow, clips[first + i].data(), kWindow * sizeof(float));
   return staging.data();
 }
+const int16_t* stage16(std::vector<std::vector<int16_t>>& clips, size_t first, size_t n, std::vector<int16_t>& staging) {
+  for (size_t i = 0; i < n; ++i) clips[first + i].resize(kWindow, 0);
+  if (n == 1) return clips[first].data();
+  staging.resize(n * kWindow);
+  for (size_t i = 0; i < n; ++i) std::memcpy(staging.data() + i * kWindow, clips[first + i].data(), kWindow * sizeof(int16_t));
+  return staging.data();
+}
 }  // namespace
 
 Monolith::Monolith(const std::string& model_prefix, const std::string& vocab_path, bool multilingual)
@@ -341,25 +356,26 @@ Monolith::Monolith(const std::string& model_prefix, const std::string& vocab_pat
   whisper_->set_filters(filters_);
 }
 
-std::vector<std::vector<int32_t>> Monolith::transcribe_tokens(std::vector<std::vector<float>>& clips) {
+std::vector<int64_t> Monolith::prompt() const {
   // What HF generate() was forced to start with inside the monolithic graph (export/generate.py:24-30):
   // English-only models start [sot, notimestamps] (cf. kGoldenGeneratedIDs, whisper.h:27-32); multilingual ones
   // carry the language and task tags, for which the reference's only statement is Decoder::forward's prompt.
-  std::vector<int64_t> prompt;
-  if (multilingual_)
-    prompt = {vocab_.token_sot, 50259 + language_id("de"), vocab_.token_transcribe, vocab_.token_not};
-  else
-    prompt = {vocab_.token_sot, vocab_.token_not};
+  if (!multilingual_) return {vocab_.token_sot, vocab_.token_not};
+  return {vocab_.token_sot, 50259 + language_id(options_.language),
+          options_.translate ? vocab_.token_translate : vocab_.token_transcribe, vocab_.token_not};
+}
+
+namespace {
+// one device call per `cap` clips; `call` = wt_transcribe_tokens or its int16 twin on the staged batch
+template <class Sample, class Stage, class Call>
+std::vector<std::vector<int32_t>> monolith_tokens(std::vector<std::vector<Sample>>& clips, size_t cap, Stage stage_fn, Call call) {
   constexpr int kMaxTotal = WT_MAX_TOKENS;
   std::vector<std::vector<int32_t>> out(clips.size());
-  const size_t cap = static_cast<size_t>(whisper_->max_batch());
   std::vector<int32_t> ids(cap * kMaxTotal), lens(cap);
   for (size_t first = 0; first < clips.size(); first += cap) {
     const size_t n = std::min(cap, clips.size() - first);
-    const float* pcm = stage(clips, first, n, staging_);
-    if (wt_transcribe_tokens(whisper_->handle(), pcm, static_cast<int>(n), kWindow, WT_HOST, prompt.data(),
-                             static_cast<int>(prompt.size()), kMaxTotal, vocab_.token_eot, ids.data(), lens.data(),
-                             WT_HOST) != WT_OK) {
+    const Sample* pcm = stage_fn(clips, first, n);
+    if (call(pcm, static_cast<int>(n), ids.data(), lens.data()) != WT_OK) {
       fprintf(stderr, "Monolith::transcribe: %s\n", wt_last_error());
       return {};  // soft failure -> empty result, like `return ""` at whisper.cpp:719-721
     }
@@ -367,12 +383,43 @@ std::vector<std::vector<int32_t>> Monolith::transcribe_tokens(std::vector<std::v
   }
   return out;
 }
+}  // namespace
+
+std::vector<std::vector<int32_t>> Monolith::transcribe_tokens(std::vector<std::vector<float>>& clips) {
+  const std::vector<int64_t> p = prompt();
+  return monolith_tokens(
+      clips, static_cast<size_t>(whisper_->max_batch()),
+      [&](std::vector<std::vector<float>>& c, size_t first, size_t n) { return stage(c, first, n, staging_); },
+      [&](const float* pcm, int n, int32_t* ids, int32_t* lens) {
+        return wt_transcribe_tokens(whisper_->handle(), pcm, n, kWindow, WT_HOST, p.data(), static_cast<int>(p.size()),
+                                    WT_MAX_TOKENS, vocab_.token_eot, ids, lens, WT_HOST);
+      });
+}
+
+std::vector<std::vector<int32_t>> Monolith::transcribe_tokens_i16(std::vector<std::vector<int16_t>>& clips) {
+  const std::vector<int64_t> p = prompt();
+  return monolith_tokens(
+      clips, static_cast<size_t>(whisper_->max_batch()),
+      [&](std::vector<std::vector<int16_t>>& c, size_t first, size_t n) { return stage16(c, first, n, staging16_); },
+      [&](const int16_t* pcm, int n, int32_t* ids, int32_t* lens) {
+        return wt_transcribe_tokens_i16(whisper_->handle(), pcm, n, kWindow, WT_HOST, p.data(), static_cast<int>(p.size()),
+                                        WT_MAX_TOKENS, vocab_.token_eot, ids, lens, WT_HOST);
+      });
+}
 
 std::vector<std::string> Monolith::transcribe_batch(std::vector<std::vector<float>>& clips) {
   const auto tokens = transcribe_tokens(clips);
   std::vector<std::string> text(clips.size());
   for (size_t i = 0; i < tokens.size(); ++i)
-    text[i] = decode(vocab_, tokens[i].data(), tokens[i].data() + tokens[i].size(), /*omit_special_tokens=*/false);
+    text[i] = decode(vocab_, tokens[i].data(), tokens[i].data() + tokens[i].size(), options_.omit_special_tokens);
+  return text;
+}
+
+std::vector<std::string> Monolith::transcribe_batch_i16(std::vector<std::vector<int16_t>>& clips) {
+  const auto tokens = transcribe_tokens_i16(clips);
+  std::vector<std::string> text(clips.size());
+  for (size_t i = 0; i < tokens.size(); ++i)
+    text[i] = decode(vocab_, tokens[i].data(), tokens[i].data() + tokens[i].size(), options_.omit_special_tokens);
   return text;
 }
 
@@ -400,23 +447,42 @@ EncDec::EncDec(const std::string& model_prefix, const std::string& vocab_path, b
   atom_->set_filters(filters_);
 }
 
-std::vector<std::string> EncDec::transcribe_batch(std::vector<std::vector<float>>& clips) {
+namespace {
+// log_mel_spectrogram -> Encoder::forward -> Decoder::forward (whisper.cpp:756-765) per batch of `cap` clips; the mel
+// and the encoder states stay on the device between the three calls. `mel` = wt_log_mel or its int16 twin.
+template <class Sample, class Stage, class MelCall>
+std::vector<std::string> encdec_batch(std::vector<std::vector<Sample>>& clips, size_t cap, Stage stage_fn, MelCall mel,
+                                      Encoder& encoder, Decoder& decoder, const Vocab& vocab, bool omit_special) {
   std::vector<std::string> text(clips.size());
-  const size_t cap = static_cast<size_t>(atom_->max_batch());
   for (size_t first = 0; first < clips.size(); first += cap) {
     const size_t n = std::min(cap, clips.size() - first);
-    const float* pcm = stage(clips, first, n, staging_);
-    // log_mel_spectrogram -> Encoder::forward -> Decoder::forward (whisper.cpp:756-765); the mel and the
-    // encoder states stay on the device between the three calls
-    if (wt_log_mel(atom_->handle(), pcm, static_cast<int>(n), kWindow, WT_HOST, nullptr, WT_DEVICE) != WT_OK) {
+    const Sample* pcm = stage_fn(clips, first, n);
+    if (mel(pcm, static_cast<int>(n)) != WT_OK) {
       std::cerr << "Failed to compute mel_ spectrogram" << '\n';  // whisper.cpp:759-761
       return std::vector<std::string>(clips.size());
     }
-    const EncoderOut enc = encoder_.forward_resident(static_cast<int>(n));
-    const auto generated = decoder_.forward_batch(enc);
-    for (size_t i = 0; i < n; ++i) text[first + i] = decode(vocab_, generated[i], /*omit_special_tokens=*/false);
+    const EncoderOut enc = encoder.forward_resident(static_cast<int>(n));
+    const auto generated = decoder.forward_batch(enc);
+    for (size_t i = 0; i < n; ++i) text[first + i] = decode(vocab, generated[i], omit_special);
   }
   return text;
+}
+}  // namespace
+
+std::vector<std::string> EncDec::transcribe_batch(std::vector<std::vector<float>>& clips) {
+  return encdec_batch(
+      clips, static_cast<size_t>(atom_->max_batch()),
+      [&](std::vector<std::vector<float>>& c, size_t first, size_t n) { return stage(c, first, n, staging_); },
+      [&](const float* pcm, int n) { return wt_log_mel(atom_->handle(), pcm, n, kWindow, WT_HOST, nullptr, WT_DEVICE); },
+      encoder_, decoder_, vocab_, options_.omit_special_tokens);
+}
+
+std::vector<std::string> EncDec::transcribe_batch_i16(std::vector<std::vector<int16_t>>& clips) {
+  return encdec_batch(
+      clips, static_cast<size_t>(atom_->max_batch()),
+      [&](std::vector<std::vector<int16_t>>& c, size_t first, size_t n) { return stage16(c, first, n, staging16_); },
+      [&](const int16_t* pcm, int n) { return wt_log_mel_i16(atom_->handle(), pcm, n, kWindow, WT_HOST, nullptr, WT_DEVICE); },
+      encoder_, decoder_, vocab_, options_.omit_special_tokens);
 }
 
 std::string EncDec::transcribe(std::vector<float>& samples) {

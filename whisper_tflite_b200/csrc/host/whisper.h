@@ -10,7 +10,9 @@
 //   * model files: `<prefix>.b200w` in place of `<prefix>.tflite` / `.encoder.tflite` / `.decoder.tflite`
 //     (whisper.cpp:669, :743-744); the vocab+filters blob is read exactly as before;
 //   * ADDED (the reference API is batch-1, whisper.cpp:368): Engine::transcribe_batch, which is what the
-//     batch-64 metric drives.
+//     batch-64 metric drives; Engine::transcribe_batch_i16 (16-bit samples as a WAV holds them, converted on the
+//     device); Engine::set_language / set_task / set_omit_special_tokens for what the reference hard-codes
+//     (language "de": whisper.cpp:327; omit_special_tokens = false: :733, :766). Defaults = the reference's.
 #pragma once
 
 #include <cstdint>
@@ -121,18 +123,28 @@ struct Encoder {
   std::shared_ptr<Atom> atom_;
 };
 
+// What the reference fixes at compile time, as run-time options with the reference's values as defaults.
+struct DecodeOptions {
+  std::string language = "de";       // whisper.cpp:327 (language tag token = 50259 + language_id(language))
+  bool translate = false;            // task token: vocab.token_transcribe (:336) or vocab.token_translate
+  bool omit_special_tokens = false;  // decode(..., omit_special_tokens) at whisper.cpp:733, :766
+};
+
 struct Decoder {
  public:
   Decoder(std::shared_ptr<Atom> atom, const whisper::Vocab& vocab) : atom_(std::move(atom)), vocab_(vocab) {}
   // whisper.cpp:314-403 for clip 0; prompt + generated ids, <= 31 entries.
   std::vector<int64_t> forward(EncoderOut encoder_out);
   std::vector<std::vector<int64_t>> forward_batch(EncoderOut encoder_out);
-  // [sot, 50259 + language_id("de"), transcribe, notimestamps] (whisper.cpp:327-339)
+  // [sot, 50259 + language_id(language), transcribe | translate, notimestamps] (whisper.cpp:327-339; "de" and
+  // transcribe unless set_options changed them)
   std::vector<int64_t> prompt() const;
+  void set_options(const DecodeOptions& o) { options_ = o; }
 
  private:
   std::shared_ptr<Atom> atom_;
   const whisper::Vocab& vocab_;
+  DecodeOptions options_;
 };
 
 struct Engine {
@@ -140,7 +152,21 @@ struct Engine {
   virtual std::string transcribe(const char* waveFile) = 0;
   // ADDED: one call for many windows; every vector is resized to 480000 like the single-clip call does.
   virtual std::vector<std::string> transcribe_batch(std::vector<std::vector<float>>& clips) = 0;
+  // ADDED: the same on 16-bit PCM (what wav_read_legacy / wav_read read before their `/ INT16_MAX`, wav_util.cpp:63-76):
+  // clips are resized to 480000 samples, the conversion runs in the mel kernel's staging load.
+  virtual std::vector<std::string> transcribe_batch_i16(std::vector<std::vector<int16_t>>& clips) = 0;
   virtual ~Engine() = default;
+
+  // ADDED: language / task / detokeniser options (defaults = the reference's hard-coded choices).
+  // set_language returns false (and changes nothing) for a code that is not in language_meta.
+  bool set_language(const std::string& code);
+  void set_task(bool translate) { options_.translate = translate; on_options(); }
+  void set_omit_special_tokens(bool omit) { options_.omit_special_tokens = omit; on_options(); }
+  const DecodeOptions& options() const { return options_; }
+
+ protected:
+  virtual void on_options() {}
+  DecodeOptions options_;
 };
 
 // Upper bound on clips per device call for engines built through the reference constructors; override with the
@@ -153,10 +179,14 @@ struct Monolith : public Engine {
   std::string transcribe(std::vector<float>& samples) final;
   std::string transcribe(const char* waveFile) final;
   std::vector<std::string> transcribe_batch(std::vector<std::vector<float>>& clips) final;
+  std::vector<std::string> transcribe_batch_i16(std::vector<std::vector<int16_t>>& clips) final;
   // ADDED: token ids of the fused PCM -> ids call (the monolithic graph's int32 output, whisper.cpp:727-732)
   std::vector<std::vector<int32_t>> transcribe_tokens(std::vector<std::vector<float>>& clips);
+  std::vector<std::vector<int32_t>> transcribe_tokens_i16(std::vector<std::vector<int16_t>>& clips);
 
  private:
+  std::vector<int64_t> prompt() const;
+  std::vector<int16_t> staging16_;
   MmapFile vocab_file_;
   Vocab vocab_;
   Filters filters_;
@@ -171,8 +201,13 @@ struct EncDec : public Engine {
   std::string transcribe(std::vector<float>& samples) final;
   std::string transcribe(const char* waveFile) final;
   std::vector<std::string> transcribe_batch(std::vector<std::vector<float>>& clips) final;
+  std::vector<std::string> transcribe_batch_i16(std::vector<std::vector<int16_t>>& clips) final;
+
+ protected:
+  void on_options() final { decoder_.set_options(options_); }
 
  private:
+  std::vector<int16_t> staging16_;
   MmapFile vocab_file_;
   Vocab vocab_;
   Filters filters_;

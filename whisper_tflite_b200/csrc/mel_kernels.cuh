@@ -42,7 +42,9 @@ constexpr int kOutStride = 34;      // floats per mel row in the output stage (3
 constexpr int kMaxMel = 128;
 
 struct MelParams {
-  const float* pcm;        // [B][n_samples]
+  const float* pcm;        // [B][n_samples] f32, or null when pcm_i16 is given
+  const short* pcm_i16;    // [B][n_samples] int16: converted like wav_read_legacy / wav_read do on the host,
+                           // static_cast<float>(s) / static_cast<float>(INT16_MAX) (wav_util.cpp:70-73, :120-122)
   float* raw;              // [B][n_mel][n_len]  log10 mel before the per-clip clamp
   int* clip_max;           // [B] ordered-int encoded max of raw (init INT_MIN)
   const float* hann;       // [400] f32 of double 0.5*(1-cos(2*pi*i/400))  (whisper.cpp:117-120)
@@ -198,10 +200,34 @@ __global__ void __launch_bounds__(kMelThreads, 2) mel_frames_kernel(MelParams p)
   const int clip = blockIdx.y;
   const int lane16 = tid & 15;   // residue r in phases A/B, k' in phase C, mel-row phase in D
   const int fslot = tid >> 4;    // frame slot 0..15 within a round
-  const float* pcm = p.pcm + (size_t)clip * p.n_samples;
   const int base = tile * kTileFrames * kHop;
 
   // ---- stage PCM span (zero fill past the clip end: whisper.cpp:149-153) ----
+  if (p.pcm_i16 != nullptr) {
+    // int16 ingest: 8 samples per 128-bit load; the division is the host's, so the mel is bit-equal to the f32 path
+    // on the converted samples
+    const short* pcm16 = p.pcm_i16 + (size_t)clip * p.n_samples;
+    const bool vec16 = ((p.n_samples & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.pcm_i16) & 15) == 0);
+    if (vec16) {
+      for (int i8 = tid; i8 < kSpan / 8; i8 += kMelThreads) {
+        const int i = i8 * 8;
+        alignas(16) short v[8];
+        if (base + i + 7 < p.n_samples) {
+          *reinterpret_cast<uint4*>(v) = *reinterpret_cast<const uint4*>(pcm16 + base + i);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = (base + i + j < p.n_samples) ? pcm16[base + i + j] : (short)0;
+        }
+        // 8 consecutive samples never straddle a hop boundary (160 = 8 * 20): one skew for all of them
+        float* dst = s_pcm + pcm_phys(i);
+        *reinterpret_cast<float4*>(dst) = make_float4((float)v[0] / 32767.0f, (float)v[1] / 32767.0f, (float)v[2] / 32767.0f, (float)v[3] / 32767.0f);
+        *reinterpret_cast<float4*>(dst + 4) = make_float4((float)v[4] / 32767.0f, (float)v[5] / 32767.0f, (float)v[6] / 32767.0f, (float)v[7] / 32767.0f);
+      }
+    } else {
+      for (int i = tid; i < kSpan; i += kMelThreads) s_pcm[pcm_phys(i)] = (base + i < p.n_samples) ? (float)pcm16[base + i] / 32767.0f : 0.0f;
+    }
+  } else {
+  const float* pcm = p.pcm + (size_t)clip * p.n_samples;
   const bool vec_ok = ((p.n_samples & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.pcm) & 15) == 0);
   if (vec_ok) {
     for (int i4 = tid; i4 < kSpan / 4; i4 += kMelThreads) {
@@ -218,6 +244,7 @@ __global__ void __launch_bounds__(kMelThreads, 2) mel_frames_kernel(MelParams p)
     }
   } else {
     for (int i = tid; i < kSpan; i += kMelThreads) s_pcm[pcm_phys(i)] = (base + i < p.n_samples) ? pcm[base + i] : 0.0f;
+  }
   }
 
   // ---- per-lane constants: Hann for this residue, W_400^{r k'} ----

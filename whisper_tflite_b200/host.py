@@ -174,6 +174,26 @@ class HostEngine:
         parts = buf.raw[:n].split(b"\0")
         return parts[:pcm.shape[0]]
 
+    def transcribe_batch_i16(self, pcm16: np.ndarray):
+        """16-bit samples [n_clips][n_samples] (converted on the device: wav_util.cpp:70-73's `/ INT16_MAX`)."""
+        pcm16 = np.ascontiguousarray(pcm16, dtype=np.int16)
+        cap = 1 << 20
+        buf = ctypes.create_string_buffer(cap)
+        n = self.lib.wth_engine_transcribe_batch_i16(self.h, pcm16.ctypes.data_as(ctypes.c_void_p), pcm16.shape[0],
+                                                     pcm16.shape[1], buf, cap)
+        assert n >= 0
+        return buf.raw[:n].split(b"\0")[:pcm16.shape[0]]
+
+    def set_language(self, code: str) -> bool:
+        """Language tag of the prompt (reference: hard-coded "de", whisper.cpp:327). False for an unknown code."""
+        return bool(self.lib.wth_engine_set_language(self.h, code.encode()))
+
+    def set_task(self, translate: bool):
+        self.lib.wth_engine_set_task(self.h, int(translate))
+
+    def set_omit_special_tokens(self, omit: bool):
+        self.lib.wth_engine_set_omit_special_tokens(self.h, int(omit))
+
     def close(self):
         if self.h:
             self.lib.wth_engine_destroy(self.h)
