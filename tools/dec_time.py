@@ -1,7 +1,6 @@
-"""Untraced time of the decoder stage (CUDA events around the launch) for the bench workload: min/median of N passes.
-usage: python tools/dec_time.py [size] [B] [passes]"""
+"""Decoder launch time alone (tiny, B clips, given clips per cluster), stage profiler.
+usage: [WT_DEC_CLUSTER=8] [WT_DEC_KV_AHEAD=n] python tools/dec_time.py [size] [B] [clips per cluster]"""
 import os
-import subprocess
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -13,22 +12,18 @@ from whisper_tflite_b200 import capi, synth  # noqa: E402
 
 size = sys.argv[1] if len(sys.argv) > 1 else "tiny"
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 64
-N = int(sys.argv[3]) if len(sys.argv) > 3 else 7
 bench.MODEL = size
 eng = capi.Engine(bench.ensure_weights(size), max_batch=B)
+if len(sys.argv) > 3:
+    eng.set_decoder_group(int(sys.argv[3]))
 pcm = torch.from_numpy(synth.synth_pcm(B, seed=0)).cuda()
 ids = torch.empty(B, 31, dtype=torch.int32, device="cuda")
 lens = torch.empty(B, dtype=torch.int32, device="cuda")
+for _ in range(2):
+    eng.transcribe_tokens(pcm, ids_out=ids, lens_out=lens)
+eng.profile(True)
 for _ in range(3):
     eng.transcribe_tokens(pcm, ids_out=ids, lens_out=lens)
-ts = []
-for _ in range(N):
-    eng.profile(True)
-    eng.transcribe_tokens(pcm, ids_out=ids, lens_out=lens)
-    st = eng.profile_read()
-    eng.profile(False)
-    ts.append(st["dec_persistent"][0])
-ts.sort()
-clk = subprocess.run(["nvidia-smi", "--query-gpu=clocks.sm,clocks.max.sm", "--format=csv,noheader"], capture_output=True,
-                     text=True).stdout.strip()
-print(f"decoder {size} B={B}: min {ts[0]:.3f} ms  median {ts[len(ts)//2]:.3f} ms  (sm clocks now/max: {clk})  ids sum {int(ids.sum())}")
+st = eng.profile_read()
+print(f"cluster={os.environ.get('WT_DEC_CLUSTER', '16')} kv_ahead={os.environ.get('WT_DEC_KV_AHEAD', 'default')} group={sys.argv[3] if len(sys.argv) > 3 else 'auto'}: "
+      f"decoder {st['dec_persistent'][0] / 3:.3f} ms; ids checksum {int(ids.sum().item())}")

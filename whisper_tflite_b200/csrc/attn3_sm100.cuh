@@ -70,6 +70,18 @@ __device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, u
       : "memory");
 }
 
+#ifndef AT3_PROBE
+#define AT3_PROBE 0   // timing probes (results are WRONG): 1 = no MUFU (p = x), 2 = only the first S piece is loaded
+#endif
+#ifndef AT3_EXP
+#define AT3_EXP 0     // 0 = ex2.approx.ftz.f32 per element; 1 = ex2.approx.ftz.bf16x2 per PAIR of elements
+#endif
+__device__ __forceinline__ uint32_t ex2_bf16x2(uint32_t x) {
+  uint32_t y;
+  asm("ex2.approx.ftz.bf16x2 %0, %1;" : "=r"(y) : "r"(x));
+  return y;
+}
+
 // One 32-key piece of a row: P = exp2(s*c - m_ref) -> 16 packed bf16 pairs (in place in v[0..15]); row-sum and maximum.
 template <bool kMasked>
 __device__ __forceinline__ void at3_piece(uint32_t (&v)[32], int c, float c_scale, float m_ref, int valid, float& l_blk,
@@ -78,8 +90,26 @@ __device__ __forceinline__ void at3_piece(uint32_t (&v)[32], int c, float c_scal
 #pragma unroll
   for (int i = 0; i < 32; i += 2) {
     const float s0 = __uint_as_float(v[i]), s1 = __uint_as_float(v[i + 1]);
+#if AT3_EXP == 1
+    // exponent arguments rounded to bf16 (|x| * 2^-9 absolute: at most 7e-4 of the row's largest weight), ONE MUFU op
+    // per pair, the result is the packed P itself; the row sum adds the bf16 values PV multiplies by
+    uint32_t pk = ex2_bf16x2(pack_bf16x2(fmaf(s0, c_scale, -m_ref), fmaf(s1, c_scale, -m_ref)));
+    if (kMasked) {
+      if (c * 32 + i >= valid) pk &= 0xffff0000u; else mx = fmaxf(mx, s0);
+      if (c * 32 + i + 1 >= valid) pk &= 0x0000ffffu; else mx = fmaxf(mx, s1);
+    } else {
+      mx = fmaxf(fmaxf(mx, s0), s1);
+    }
+    la += __uint_as_float(pk << 16);
+    lb += __uint_as_float(pk & 0xffff0000u);
+    v[i >> 1] = pk;
+#else
+#if AT3_PROBE == 1
+    float p0 = fmaf(s0, c_scale, -m_ref), p1 = fmaf(s1, c_scale, -m_ref);
+#else
     float p0 = ex2_approx(fmaf(s0, c_scale, -m_ref));
     float p1 = ex2_approx(fmaf(s1, c_scale, -m_ref));
+#endif
     if (kMasked) {
       if (c * 32 + i >= valid) p0 = 0.0f; else mx = fmaxf(mx, s0);
       if (c * 32 + i + 1 >= valid) p1 = 0.0f; else mx = fmaxf(mx, s1);
@@ -89,6 +119,7 @@ __device__ __forceinline__ void at3_piece(uint32_t (&v)[32], int c, float c_scal
     la += p0;
     lb += p1;
     v[i >> 1] = pack_bf16x2(p0, p1);   // word i/2 is dead by now
+#endif
   }
   l_blk += la + lb;
 }
@@ -104,16 +135,31 @@ __device__ __forceinline__ void at3_pass2(uint32_t t_s, uint32_t t_p, float c_sc
   uint32_t va[32], vb[32];
   tmem_ld32(t_s, va);
   tmem_ld_wait();
+#if AT3_PROBE == 2
+#pragma unroll
+  for (int i = 0; i < 32; ++i) vb[i] = va[i] ^ 0x00010000u;
+#else
   tmem_ld32(t_s + 32, vb);
+#endif
   at3_piece<kMasked>(va, 0, c_scale, m_ref, valid, l_blk, mx);
   pre();
   tmem_st16(t_p, va);
   tmem_ld_wait();
+#if AT3_PROBE == 2
+#pragma unroll
+  for (int i = 0; i < 32; ++i) va[i] = vb[i] ^ 0x00020000u;
+#else
   tmem_ld32(t_s + 64, va);
+#endif
   at3_piece<kMasked>(vb, 1, c_scale, m_ref, valid, l_blk, mx);
   tmem_st16(t_p + 16, vb);
   tmem_ld_wait();
+#if AT3_PROBE == 2
+#pragma unroll
+  for (int i = 0; i < 32; ++i) vb[i] = va[i] ^ 0x00040000u;
+#else
   tmem_ld32(t_s + 96, vb);
+#endif
   at3_piece<kMasked>(va, 2, c_scale, m_ref, valid, l_blk, mx);
   tmem_st16(t_p + 32, va);
   tmem_ld_wait();

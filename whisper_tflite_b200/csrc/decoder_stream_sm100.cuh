@@ -67,6 +67,7 @@ struct DsParams {
   int upw;                        // weight units per warp and ring stage (6 for d = 384, 8 for d = 512 / 768)
   int n_stages;                   // ring depth (host: what fits next to the activation tiles)
   int debug;
+  int kv_ahead;                   // K/V chunks the L2 prefetch runs ahead of the shared-memory copies (0 = off)
   const uint4* w_logits;          // packed tied embedding (final LayerNorm gain folded in)
   const float* b_logits;          // [V] tok_emb . lnf_beta
   const __nv_bfloat16* tok_emb;   // [V][d] (embedding lookups)
@@ -93,6 +94,9 @@ struct DsStream {
   int cpp;                          // K/V chunks per pair
   volatile int stop;                // consumers -> producer: leave after draining
   volatile unsigned consumed;       // ring stages consumed when `stop` was raised
+  int lg_tiles, lg_row0, lg_row1;   // logits: 128-row tiles of this CTA's vocabulary slice [lg_row0, lg_row1)
+  unsigned tmem_addr;               // 32 tensor-memory columns: two 128 x 16 f32 logits accumulators
+  unsigned long long lg_bar[4];     // mbarriers: accumulator full [2] (tcgen05.commit), accumulator drained [2] (4 epilogue warps)
 };
 
 // Shared memory. Activations never go through global memory between phases: every CTA holds a full copy of the
@@ -114,6 +118,9 @@ struct DsSmem {
   __host__ __device__ static constexpr int h_stride(int d) { return 8 * d + 64; }   // == 64 mod 128
   __host__ __device__ static constexpr int a_off(int d) { return (kX + kDsRows * x_stride(d) + 127) & ~127; }
   __host__ __device__ static constexpr int h_off(int d) { return a_off(d) + kDsRows * a_stride(d); }
+  // logits B operand (ds_logits): [d / 64 blocks][16 clips][128 B], inside the hidden-state tile; the 128-byte swizzle is a
+  // function of ADDRESS bits 7..9, so the operand starts on a 1024-byte boundary
+  __host__ __device__ static constexpr int lb_off(int d) { return (h_off(d) + 1023) & ~1023; }
   __host__ __device__ static constexpr int ring(int d) { return (h_off(d) + kDsRows * h_stride(d) + 1023) & ~1023; }
   __host__ __device__ static constexpr int total(int d, int n_stages) { return ring(d) + n_stages * kDsStageBytes; }
 };
@@ -136,6 +143,9 @@ constexpr bool kDsProbe = true;   // -DDS_PROBE: WT_DEC_DEBUG=4 / 8 skip the cro
 constexpr bool kDsProbe = false;
 #endif
 __device__ __forceinline__ void ds_cons_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kDsConsThreads) : "memory"); }
+__device__ __forceinline__ void l2_prefetch(const void* gsrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ uint64_t l2_evict_last_policy() {
   uint64_t p;
   asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
@@ -192,7 +202,9 @@ __device__ __forceinline__ void ds_pair_owner(const DsStream* st, int pr, int& c
 __device__ __forceinline__ void ds_cluster_sync(uint8_t* smem, const DsParams& p, unsigned& cphase, int kind,
                                                 unsigned long long& tlast, int G, bool tr) {
   const unsigned long long t_arr = tr ? dec_globaltimer() : 0ull;
+#ifndef DS_NO_FENCE
   asm volatile("fence.acq_rel.cluster;" ::: "memory");
+#endif
 #if DS_TRACE_FINE
   const unsigned long long t_f = tr ? dec_globaltimer() : 0ull;
 #endif
@@ -287,6 +299,40 @@ __global__ void ds_fold_bias_kernel(const __nv_bfloat16* __restrict__ W, const f
   if (lane == 0) out[warp] = s + (b ? b[warp] : 0.0f);
 }
 
+// The tied logits matrix in the layout tcgen05.mma reads from shared memory (ds_logits): per CTA slice of the
+// vocabulary (the same 8-row-group split as above), tiles of 128 vocabulary rows; a tile = K / 64 blocks of
+// [128 rows][64 k] bf16, rows of 128 bytes, the eight 16-byte chunks of a row XOR-swizzled by (row & 7) — exactly what a
+// 128B-swizzled TMA tile load would leave, written once here so that plain bulk copies (two blocks = one 32 KB ring
+// stage) deliver MMA-ready operands. LayerNorm gain folded into the columns; rows past the slice / vocabulary are zero.
+__host__ __device__ inline int ds_logit_rows_per_cta(int V, int G) { return (((V + 7) / 8 + G - 1) / G) * 8; }
+__host__ __device__ inline int ds_logit_tiles_per_cta(int V, int G) { return (ds_logit_rows_per_cta(V, G) + 127) / 128; }
+__global__ void ds_pack_logits_kernel(const __nv_bfloat16* __restrict__ W, const float* __restrict__ gamma,
+                                      uint4* __restrict__ out, int V, int K, int G) {
+  const int rpc = ds_logit_rows_per_cta(V, G), T = ds_logit_tiles_per_cta(V, G), nkb = K >> 6;
+  const long long total = (long long)G * T * nkb * 128 * 8;   // 16-byte chunks
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx & 7), row = (int)((idx >> 3) & 127);
+    long long rest = idx >> 10;
+    const int kb = (int)(rest % nkb);
+    rest /= nkb;
+    const int t = (int)(rest % T), r = (int)(rest / T);
+    const int n = r * rpc + t * 128 + row, k0 = kb * 64 + c * 8;
+    uint32_t o[4] = {0u, 0u, 0u, 0u};
+    if (n < V && t * 128 + row < rpc) {
+      float f[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        f[j] = __bfloat162float(W[(size_t)n * K + k0 + j]);
+        if (gamma) f[j] *= gamma[k0 + j];
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) o[j] = dec_pack2(f[2 * j], f[2 * j + 1]);
+    }
+    out[(((long long)(r * T + t) * nkb + kb) * 128 + row) * 8 + (c ^ (row & 7))] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
 
 // ---------------------------------------------------------------------------------------------------
 // LayerNorm (gain/bias folded into the packed weights) of the residual copy sX -> MMA operand tile sA, shared memory to
@@ -299,6 +345,9 @@ __device__ __forceinline__ float ds_half_sum(float v) {
   for (int o = 8; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+// kUmmaB: write the operand as the B side of tcgen05.mma instead ([16 clips][64 k] blocks of 2 KB, rows of 128 bytes,
+// 16-byte chunks XOR-swizzled by (row & 7)) into the hidden-state tile, which is idle outside fc1 / fc2.
+template <bool kUmmaB = false>
 __device__ __forceinline__ void ds_stage_norm(uint8_t* smem, int n_clips, int d) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r = warp * 2 + (lane >> 4), l16 = lane & 15;    // kDsRows == 2 * kDsConsWarps rows, one pass
@@ -331,7 +380,12 @@ __device__ __forceinline__ void ds_stage_norm(uint8_t* smem, int n_clips, int d)
     for (int i = 0; i < nv; ++i) {
       float f[8];
       bf16x8_to_f32(src[i * 16], f);
-      dst[i * 16] = make_uint4(dec_pack2((f[0] - mean) * rstd, (f[1] - mean) * rstd), dec_pack2((f[2] - mean) * rstd, (f[3] - mean) * rstd),
+      uint4* o = dst + i * 16;
+      if (kUmmaB) {
+        const int pi = i * 16 + l16;   // 16-byte piece of the row: k = 8 pi .. 8 pi + 7 -> block pi / 8, chunk pi % 8
+        o = reinterpret_cast<uint4*>(smem + DsSmem::lb_off(d) + (pi >> 3) * 2048 + r * 128 + (((pi & 7) ^ (r & 7)) << 4));
+      }
+      *o = make_uint4(dec_pack2((f[0] - mean) * rstd, (f[1] - mean) * rstd), dec_pack2((f[2] - mean) * rstd, (f[3] - mean) * rstd),
                                dec_pack2((f[4] - mean) * rstd, (f[5] - mean) * rstd), dec_pack2((f[6] - mean) * rstd, (f[7] - mean) * rstd));
     }
 }
@@ -342,6 +396,7 @@ struct DsRing {
   int slot;
   unsigned par;
   int n_stages;   // ring depth (a register copy: DsParams lives in shared memory and every barrier asm clobbers memory)
+  unsigned lt;    // logits tiles processed so far in this launch (phase of the accumulator barriers)
   __device__ __forceinline__ void advance() {
     ++cons;
     if (++slot == n_stages) { slot = 0; par ^= 1u; }
@@ -505,108 +560,110 @@ __device__ __forceinline__ void ds_embed(uint8_t* smem, const DsParams& p, int p
   }
 }
 
-// ---- final LayerNorm -> tied logits with a fused (max, last index) per row (whisper.cpp:346-361's tie rule); this
-//      CTA's winners go to every peer's s_amax[rank][row] ----
+// ---- final LayerNorm -> tied logits on tcgen05 with a fused (max, last index) per clip (whisper.cpp:346-361's tie
+//      rule); this CTA's winners go to every peer's s_amax[rank][row].
+//      The one decoder contraction with real width (N = 51 865): D[128 vocabulary rows][16 clips] = W_tile . X^T with the
+//      weights as the A operand straight out of the ring (packed MMA-ready by ds_pack_logits_kernel, two 64-wide k blocks
+//      per 32 KB stage) and the LayerNorm output as a 16-row B operand: no weight ever passes through a register. Warp 0
+//      issues (one elected lane), every consumer warp paces the ring (its arrival frees the stage; warp 0's is the
+//      tcgen05.commit), warps 4..7 drain the two accumulators (lane = vocabulary row: 16 clips' logits per thread) and
+//      keep the running winners per clip in registers — the phase runs at the rate the stream delivers the matrix. ----
 __device__ __noinline__ DsRing ds_logits(uint8_t* smem, const DsParams& p, DsRing rg, int pos) {
-  const DsStream* st = ds_stream(smem);
-  const int d = p.d, B = p.n_clips, V = p.V, as = DsSmem::a_stride(d);
-  const uint8_t* sA = smem + DsSmem::a_off(d);
+  DsStream* st = ds_stream(smem);
+  const int d = p.d, B = p.n_clips, V = p.V;
   unsigned long long* s_best = reinterpret_cast<unsigned long long*>(smem + DsSmem::kMisc);  // [16], merge scratch is idle
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid < kDsRows) s_best[tid] = 0ull;
-  ds_stage_norm(smem, B, d);
+  ds_stage_norm<true>(smem, B, d);
+  fence_proxy_async();   // the operand tile was written with ordinary stores; tcgen05.mma reads it through the async proxy
   ds_cons_bar();
-  const int ng = st->ng[DS_LOGITS], kbK = st->kbk[DS_LOGITS];
-  const int g0 = (int)(st->slice_unit0[DS_LOGITS] / kbK);
-  const int upw_f = st->upw_full[DS_LOGITS], upw_l = st->upw_last[DS_LOGITS], kph_f = kbK / upw_f, kph_l = kbK / upw_l;
-  const uint8_t* ring = smem + DsSmem::ring(d);
-  const uint8_t* a_lane = sA + (size_t)g * as + t * 16;
-  const int step = pos - (p.prompt_len - 1);
-  float* lg = p.step_logits ? p.step_logits + (size_t)step * p.step_logits_stride : nullptr;
-  const bool r0 = g < B, r1 = g + 8 < B;
-  unsigned long long best0 = 0ull, best1 = 0ull;
+  const int T = st->lg_tiles, spt = d >> 7;   // ring stages per 128-row tile (two 64-wide k blocks each)
   uint64_t* full = ds_full(smem);
   uint64_t* empty = ds_empty(smem);
-  constexpr int R = 2 * kDsConsWarps;   // 16 groups per round: warp w owns groups w and w + 8 (ds_pack_weights_kernel, gpw 2)
-  for (int rho = 0; rho * R < ng; ++rho) {
-    const int nact = (ng - rho * R < R) ? ng - rho * R : R;
-    const int upw = nact == R ? upw_f : upw_l, kph = nact == R ? kph_f : kph_l;
-    const int cnt = (warp < nact ? 1 : 0) + (warp + 8 < nact ? 1 : 0);       // this warp's groups in the round
-    const uint32_t w_off = (uint32_t)(ds_round_prefix(warp, nact) * upw) * kDsUnitBytes + lane * 16;
-    const int n0 = (g0 + rho * R + warp) * 8 + 2 * t, n1 = n0 + 64;          // first column of this lane in either group
-    float2 bz0 = make_float2(0.0f, 0.0f), bz1 = bz0;
-    if (cnt > 0) bz0 = __ldg(reinterpret_cast<const float2*>(p.b_logits + n0));  // padded to a multiple of 8 on the host
-    if (cnt > 1) bz1 = __ldg(reinterpret_cast<const float2*>(p.b_logits + n1));
-    float c0[4] = {0.0f, 0.0f, 0.0f, 0.0f}, c1[4] = {0.0f, 0.0f, 0.0f, 0.0f};   // group w: two chains over k
-    float e0[4] = {0.0f, 0.0f, 0.0f, 0.0f}, e1[4] = {0.0f, 0.0f, 0.0f, 0.0f};   // group w + 8
-    for (int h = 0; h < kph; ++h) {
-      mbar_wait(full + rg.slot, rg.par);
-      if (!(kDsProbe && (p.debug & 8))) {
-        const uint8_t* wp = ring + (size_t)rg.slot * kDsStageBytes + w_off;
-        const uint8_t* ap = a_lane + (size_t)(h * upw) * 64;
-        if (cnt > 1) {
-#pragma unroll 2
-          for (int u = 0; u < upw; ++u) {
-            const uint4 w0 = *reinterpret_cast<const uint4*>(wp + u * kDsUnitBytes);
-            const uint4 w1 = *reinterpret_cast<const uint4*>(wp + (upw + u) * kDsUnitBytes);
-            const uint4 lo = *reinterpret_cast<const uint4*>(ap + u * 64);
-            const uint4 hi = *reinterpret_cast<const uint4*>(ap + u * 64 + 8 * as);
-            mma_bf16_16816(c0, lo.x, hi.x, lo.y, hi.y, w0.x, w0.y);
-            mma_bf16_16816(e0, lo.x, hi.x, lo.y, hi.y, w1.x, w1.y);
-            mma_bf16_16816(c1, lo.z, hi.z, lo.w, hi.w, w0.z, w0.w);
-            mma_bf16_16816(e1, lo.z, hi.z, lo.w, hi.w, w1.z, w1.w);
-          }
-        } else if (cnt == 1) {
-#pragma unroll 2
-          for (int u = 0; u < upw; ++u) {
-            const uint4 w0 = *reinterpret_cast<const uint4*>(wp + u * kDsUnitBytes);
-            const uint4 lo = *reinterpret_cast<const uint4*>(ap + u * 64);
-            const uint4 hi = *reinterpret_cast<const uint4*>(ap + u * 64 + 8 * as);
-            mma_bf16_16816(c0, lo.x, hi.x, lo.y, hi.y, w0.x, w0.y);
-            mma_bf16_16816(c1, lo.z, hi.z, lo.w, hi.w, w0.z, w0.w);
-          }
-        }
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(empty + rg.slot);
-      rg.advance();
-    }
+  uint64_t* acc_full = reinterpret_cast<uint64_t*>(st->lg_bar);
+  uint64_t* acc_empty = acc_full + 2;
+  const uint32_t tmem = st->tmem_addr;
+  const uint32_t ring = smem_u32(smem + DsSmem::ring(d)), sb = smem_u32(smem + DsSmem::lb_off(d));
+  constexpr uint32_t idesc = make_idesc_bf16(128, 16);
+  const int step = pos - (p.prompt_len - 1);
+  float* lg = p.step_logits ? p.step_logits + (size_t)step * p.step_logits_stride : nullptr;
+  unsigned long long best[kDsRows];
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      if (j >= cnt) break;
-      const int n = j ? n1 : n0;
-      const float2 bz = j ? bz1 : bz0;
-      const float v00 = (j ? e0[0] + e1[0] : c0[0] + c1[0]) + bz.x, v01 = (j ? e0[1] + e1[1] : c0[1] + c1[1]) + bz.y;
-      const float v10 = (j ? e0[2] + e1[2] : c0[2] + c1[2]) + bz.x, v11 = (j ? e0[3] + e1[3] : c0[3] + c1[3]) + bz.y;
-      if (n < V) {
-        if (r0) best0 = u64_max(best0, pack_val_idx(v00, (unsigned)n));
-        if (r1) best1 = u64_max(best1, pack_val_idx(v10, (unsigned)n));
+  for (int c = 0; c < kDsRows; ++c) best[c] = 0ull;
+  // Roles (decoupled, so that nothing but the MMAs' own completion holds a ring stage): warp 0 issues, warp 1 paces the
+  // ring for the seven warps that never touch the stage (its arrival counts 7; warp 0's is the tcgen05.commit), warps
+  // 4..7 only drain accumulators. Every thread advances its copy of the ring position by the same T * spt stages.
+  const bool probe = (p.debug & 16) != 0;   // WT_DEC_DEBUG=16: stream-rate probe (no MMAs; results are wrong)
+  if (warp == 0) {
+    DsRing r = rg;
+    for (int t = 0; t < T; ++t, ++r.lt) {
+      const unsigned acc = r.lt & 1u, use = r.lt >> 1;
+      if (!probe) {   // the accumulator's previous tile has been drained (a fresh barrier passes the first two uses)
+        mbar_wait(acc_empty + acc, (use & 1u) ^ 1u);
+        tc_fence_after();
       }
-      if (n + 1 < V) {
-        if (r0) best0 = u64_max(best0, pack_val_idx(v01, (unsigned)(n + 1)));
-        if (r1) best1 = u64_max(best1, pack_val_idx(v11, (unsigned)(n + 1)));
-      }
-      if (lg) {
-        if (r0) {
-          float* row = lg + (size_t)(p.clip0 + g) * V;
-          if (n < V) row[n] = v00;
-          if (n + 1 < V) row[n + 1] = v01;
+      for (int s_ = 0; s_ < spt; ++s_) {
+        mbar_wait(full + r.slot, r.par);
+        tc_fence_after();
+        if (probe) {
+          if (lane == 0) mbar_arrive(empty + r.slot);
+        } else if (elect_one()) {
+          const uint32_t sa = ring + (uint32_t)r.slot * kDsStageBytes;
+#pragma unroll
+          for (int kb2 = 0; kb2 < 2; ++kb2) {
+            const uint64_t da = make_sw128_desc(sa + kb2 * 16384), db = make_sw128_desc(sb + (s_ * 2 + kb2) * 2048);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_bf16(tmem + acc * 16, da + 2 * k, db + 2 * k, idesc, (s_ | kb2 | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(empty + r.slot);                       // this warp's arrival: the stage is free once the MMAs retire
+          if (s_ == spt - 1) umma_commit(acc_full + acc);
         }
-        if (r1) {
-          float* row = lg + (size_t)(p.clip0 + g + 8) * V;
-          if (n < V) row[n] = v10;
-          if (n + 1 < V) row[n + 1] = v11;
+        __syncwarp();
+        r.advance();
+      }
+    }
+  } else if (warp == 1) {
+    DsRing r = rg;
+    for (int i = 0; i < T * spt; ++i) {
+      mbar_wait(full + r.slot, r.par);   // the stage's current use has begun: the arrival cannot land in an earlier phase
+      if (lane == 0)
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(empty + r.slot)), "r"(kDsConsWarps - 1) : "memory");
+      r.advance();
+    }
+  } else if (warp >= 4 && !probe) {
+    unsigned lt = rg.lt;
+    for (int t = 0; t < T; ++t, ++lt) {
+      const unsigned acc = lt & 1u, use = lt >> 1;
+      mbar_wait(acc_full + acc, use & 1u);
+      tc_fence_after();
+      uint32_t v[16];
+      tmem_ld16(tmem + ((uint32_t)((warp & 3) * 32) << 16) + acc * 16, v);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty + acc);
+      const int n = st->lg_row0 + t * 128 + (warp & 3) * 32 + lane;
+      if (n < st->lg_row1 && n < V) {
+        const float bz = __ldg(p.b_logits + n);
+#pragma unroll
+        for (int c = 0; c < kDsRows; ++c) {
+          if (c < B) {
+            const float val = __uint_as_float(v[c]) + bz;
+            best[c] = u64_max(best[c], pack_val_idx(val, (unsigned)n));
+            if (lg) lg[(size_t)(p.clip0 + c) * V + n] = val;
+          }
         }
       }
     }
   }
-  best0 = u64_max(best0, __shfl_xor_sync(0xffffffffu, best0, 1));
-  best0 = u64_max(best0, __shfl_xor_sync(0xffffffffu, best0, 2));
-  best1 = u64_max(best1, __shfl_xor_sync(0xffffffffu, best1, 1));
-  best1 = u64_max(best1, __shfl_xor_sync(0xffffffffu, best1, 2));
-  if (t == 0) {
-    if (best0 != 0ull) atomicMax(s_best + g, best0);
-    if (best1 != 0ull) atomicMax(s_best + g + 8, best1);
+  for (int i = 0; i < T * spt; ++i) rg.advance();
+  rg.lt += (unsigned)T;
+  if (warp >= 4) {
+#pragma unroll
+    for (int c = 0; c < kDsRows; ++c) {
+      const unsigned long long m = warp_max_u64(best[c]);
+      if (lane == 0 && m != 0ull) atomicMax(s_best + c, m);
+    }
   }
   ds_cons_bar();
   if (tid < B) ds_push_all(smem_u32(smem + DsSmem::kAmax) + (p.rank * kDsRows + tid) * 8, s_best[tid], p.G);
@@ -707,7 +764,8 @@ __device__ __forceinline__ void ds_ldsm4_t(uint32_t addr, uint32_t (&r)[4]) {
 // m16n8k16 with only row 0 of A alive (one query per (clip, head) pair): rows 8..15 of A are zero and their
 // accumulators are dead, so the instruction carries two live accumulator registers instead of four
 __device__ __forceinline__ void ds_mma_row0(float& c0, float& c1, uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
-  float d2, d3;
+  float d2, d3;   // dead accumulators of the zero rows
+  (void)d2; (void)d3;
   asm volatile(
       "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%5}, {%7,%8}, {%0,%1,%9,%9};"
       : "+f"(c0), "+f"(c1), "=f"(d2), "=f"(d3)
@@ -930,6 +988,7 @@ __device__ __noinline__ unsigned ds_producer(uint8_t* smem, const DsParams& p) {
   const uint64_t pol_kv = l2_evict_first_policy(), pol_w = l2_evict_last_policy();
   const int pair0 = pr.st->pair0, npairs = pr.st->npairs, cpp = pr.st->cpp;
   const size_t chunk_elems = (size_t)2 * kXaChunk * 64;
+  const int ahead = p.kv_ahead;
   for (int pos = 0; pos <= p.max_total - 2; ++pos) {
     for (int l = 0; l < p.n_layers; ++l) {
       const DsLayerDev& L = p.layers[l];
@@ -937,16 +996,29 @@ __device__ __noinline__ unsigned ds_producer(uint8_t* smem, const DsParams& p) {
       if (!pr.weights(L.w[DS_OUT], DS_OUT, pol_w)) return pr.n;
       if (!pr.weights(L.w[DS_XQ], DS_XQ, pol_w)) return pr.n;
       {
+        // The K/V chunks come from HBM (each is read once per position): an L2 prefetch runs kDsKvAhead chunks ahead of
+        // the copies into shared memory, so those find their lines in L2 — the <= 4 bulk copies a CTA keeps in flight
+        // then turn over at L2 latency instead of DRAM latency (the stream rate of a CTA is bytes in flight / latency).
         const __nv_bfloat16* src = L.kvx + ((size_t)p.clip0 * p.H + pair0) * cpp * chunk_elems;
-        for (int c = 0; c < npairs * cpp; ++c, src += chunk_elems)
+        const int n_ch = npairs * cpp;
+        if (ahead > 0)
+          for (int c = 0; c < ahead && c < n_ch; ++c) l2_prefetch(src + (size_t)c * chunk_elems, (uint32_t)kDsStageBytes);
+        for (int c = 0; c < n_ch; ++c, src += chunk_elems) {
+          if (ahead > 0 && c + ahead < n_ch) l2_prefetch(src + (size_t)ahead * chunk_elems, (uint32_t)kDsStageBytes);
           if (!pr.issue(src, (uint32_t)kDsStageBytes, pol_kv)) return pr.n;
+        }
       }
       if (!pr.weights(L.w[DS_XOUT], DS_XOUT, pol_w)) return pr.n;
       if (!pr.weights(L.w[DS_FC1], DS_FC1, pol_w)) return pr.n;
       if (!pr.weights(L.w[DS_FC2], DS_FC2, pol_w)) return pr.n;
     }
-    if (pos >= p.prompt_len - 1)
-      if (!pr.weights(p.w_logits, DS_LOGITS, pol_w, 2 * kDsConsWarps)) return pr.n;
+    if (pos >= p.prompt_len - 1) {   // the tied logits matrix: this CTA's tiles, 32 KB (two k blocks) per stage
+      const int spt = p.d >> 7;
+      const uint8_t* src = reinterpret_cast<const uint8_t*>(p.w_logits) +
+                           (size_t)p.rank * ds_logit_tiles_per_cta(p.V, p.G) * spt * kDsStageBytes;
+      for (int i = 0; i < pr.st->lg_tiles * spt; ++i)
+        if (!pr.issue(src + (size_t)i * kDsStageBytes, (uint32_t)kDsStageBytes, pol_w)) return pr.n;
+    }
   }
   return pr.n;
 }
@@ -997,6 +1069,14 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
     st->npairs = base + (rank < rem ? 1 : 0);
     st->pair0 = rank * base + (rank < rem ? rank : rem);
     st->cpp = (p.S + kXaChunk - 1) / kXaChunk;
+    {
+      const int rpc = ds_logit_rows_per_cta(p.V, G);
+      st->lg_row0 = rank * rpc;
+      st->lg_row1 = (rank + 1) * rpc < p.V ? (rank + 1) * rpc : p.V;
+      const int rows = st->lg_row1 - st->lg_row0;
+      st->lg_tiles = rows > 0 ? (rows + 127) / 128 : 0;
+      for (int i = 0; i < 4; ++i) mbar_init(reinterpret_cast<uint64_t*>(st->lg_bar) + i, i < 2 ? 1u : 4u);
+    }
     st->stop = 0;
     st->consumed = 0u;
     for (int i = 0; i < kDsMaxStages; ++i) {
@@ -1018,7 +1098,10 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
       *reinterpret_cast<uint4*>(ds_smem + i) = make_uint4(0u, 0u, 0u, 0u);
     }
   }
+  if (warp == 0) tmem_alloc(&ds_stream(ds_smem)->tmem_addr, 32);   // the logits accumulators (ds_logits)
+  tc_fence_before();
   __syncthreads();
+  tc_fence_after();
   // every CTA's barriers and tiles exist before any peer arrives on / pushes into them
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 
@@ -1031,7 +1114,7 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
     unsigned long long tlast = tracing ? dec_globaltimer() : 0ull;
     unsigned cphase = 0;
     DsRing rg;
-    rg.cons = 0; rg.slot = 0; rg.par = 0; rg.n_stages = p.n_stages;
+    rg.cons = 0; rg.slot = 0; rg.par = 0; rg.n_stages = p.n_stages; rg.lt = 0;
     float2 xr[2][2];
 #pragma unroll
     for (int i = 0; i < 2; ++i) xr[i][0] = xr[i][1] = make_float2(0.0f, 0.0f);
@@ -1076,7 +1159,12 @@ __global__ void __launch_bounds__(kDsThreads, 1) decoder_stream_kernel(const DsP
     const unsigned consumed = ds_stream(ds_smem)->consumed;
     for (unsigned j = consumed; j < issued; ++j) mbar_wait(ds_full(ds_smem) + (j % p.n_stages), (j / p.n_stages) & 1u);
   }
+  tc_fence_before();
   __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(ds_stream(ds_smem)->tmem_addr, 32);
+  }
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 

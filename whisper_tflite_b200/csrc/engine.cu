@@ -285,6 +285,7 @@ struct wt_engine {
   uint4* ds_w_logits = nullptr;
   float* ds_b_logits = nullptr;
   int ds_upw = 0, ds_stages = 0, ds_smem = 0;
+  int ds_kv_ahead = 0;   // L2 prefetch distance of the K/V stream in chunks (WT_DEC_KV_AHEAD, read at engine creation)
   int init_stream_weights();
   int enc_clips = 0;  // clips whose encoder states / cross K,V are resident
   std::map<std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint64_t, uint64_t, uint32_t>, CUtensorMap> map_cache;
@@ -804,6 +805,7 @@ int wt_engine::init_persistent_decoder() {
     ds_smem = wt::DsSmem::total(dims.d_model, ds_stages);
   }
   WT_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, ds_smem));
+  if (const char* ka = getenv("WT_DEC_KV_AHEAD")) ds_kv_ahead = atoi(ka) < 0 ? 0 : atoi(ka);
   // cluster shape: 16 CTAs when the device can co-schedule a 16-CTA cluster per GPC, else the portable 8.
   // WT_DEC_CLUSTER / WT_DEC_GROUP override (probing).
   dec_cluster = 0;
@@ -888,13 +890,16 @@ int wt_engine::init_stream_weights() {
     o.kc = (bf16*)L.kc; o.vc = (bf16*)L.vc;
   }
   {
-    Lin emb;
-    emb.w = tok_emb; emb.b = nullptr; emb.N = V; emb.K = d;
-    const uint4* w = nullptr;
-    const float* b = nullptr;
-    WT_TRY(pack(emb, &dec_ln, &w, &b, 2));   // two column groups per warp and round: 32 KB stages (ds_logits)
-    ds_w_logits = const_cast<uint4*>(w);
-    ds_b_logits = const_cast<float*>(b);
+    // tied logits matrix: MMA-ready tiles per CTA slice (ds_pack_logits_kernel), final LayerNorm folded in
+    const int T = wt::ds_logit_tiles_per_cta(V, G), nkb = d / 64;
+    const size_t chunks = (size_t)G * T * nkb * 128 * 8;   // 16-byte chunks
+    WT_TRY(alloc(&ds_w_logits, chunks));
+    WT_TRY(alloc(&ds_b_logits, (size_t)((V + 7) / 8) * 8, true));
+    const int blocks = (int)((chunks + 255) / 256 < 8192 ? (chunks + 255) / 256 : 8192);
+    wt::ds_pack_logits_kernel<<<blocks, 256, 0, stream>>>((const bf16*)tok_emb, dec_ln.g, ds_w_logits, V, d, G);
+    wt::ds_fold_bias_kernel<<<(V * 32 + 255) / 256, 256, 0, stream>>>((const bf16*)tok_emb, nullptr, dec_ln.b, ds_b_logits, V, d);
+    WT_CUDA_OK(cudaGetLastError());
+    launches += 2;
   }
   WT_TRY(alloc(&d_ds_layers, hl.size()));
   WT_CUDA_OK(cudaMemcpyAsync(d_ds_layers, hl.data(), hl.size() * sizeof(wt::DsLayerDev), cudaMemcpyHostToDevice, stream));
@@ -926,6 +931,7 @@ int wt_engine::decode_persistent(int n_clips, int prompt_len, int max_total, int
     q.upw = ds_upw;
     q.n_stages = ds_stages;
     if (const char* dbg = getenv("WT_DEC_DEBUG")) q.debug = atoi(dbg);
+    q.kv_ahead = ds_kv_ahead;
     q.d = d; q.H = H; q.S = S; q.V = dims.n_vocab;
     q.w_logits = ds_w_logits; q.b_logits = ds_b_logits;
     q.tok_emb = (const bf16*)tok_emb;
