@@ -278,9 +278,13 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
       int stage = 0;
       uint32_t phase = 0;
       int n_end = 0;
+      // The first tile of a CTA is its block index; every further one is drawn from the counter ONE TILE AHEAD: the
+      // atomic's round trip to L2 runs underneath the current tile's loads instead of in front of the next tile's.
+      int next_tile = (int)blockIdx.x;
       for (int it = 0;; ++it) {
-        int tile = (n_end == 0) ? atomicAdd(p.sched, 1) : n_tiles;
+        int tile = (n_end == 0) ? next_tile : n_tiles;
         if (tile >= n_tiles) tile = -1;
+        if (tile >= 0) next_tile = (int)gridDim.x + atomicAdd(p.sched, 1);
         // publish: slot it % kTileQ (free once the MMA issuer and the epilogue group of tile it - kTileQ have read it)
         const int qs = it % S::kTileQ;
         mbar_wait(bar_qempty + qs, ((uint32_t)(it / S::kTileQ) & 1u) ^ 1u);
