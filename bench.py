@@ -33,14 +33,38 @@ sys.path.insert(0, ROOT)
 
 METRIC = "RTFx (audio-sec/sec) whisper-tiny encdec, batch 64"
 UNIT = "audio-sec/sec"
-CLIPS_PER_GPU = 64
 CLIP_S = 30.0
-MODEL = "tiny"
 
-# algorithmic work per clip (DESIGN.md "Rooflines")
+# BASELINE.json configs. The driver runs the default (configs[1], the configuration the metric is quoted on); the others
+# print the same line format for the record (profiles/r02_configs.jsonl).
+CONFIGS = {
+    "tiny64": {"model": "tiny", "clips": 64, "workload": "BASELINE.json configs[1]: whisper-tiny (multilingual vocab 51865, language "
+               "tag de) log-mel + encoder + greedy decode (4 prompt + <=27 new tokens), 64 synthetic 30 s clips per GPU, "
+               "seeded random-init weights"},
+    "long1h": {"model": "tiny", "clips": 64, "stream_windows": 120, "repeat": 32, "workload": "BASELINE.json configs[2]: whisper-tiny, "
+               "one call per batch (monolith path: PCM in, ids out), 1 h of synthetic audio = 120 windows of 30 s, the hour "
+               "repeated x32 (3840 windows) and sharded contiguously by window over the GPUs, batches of 64"},
+    "base256": {"model": "base", "clips": 256, "workload": "BASELINE.json configs[3]: whisper-base architecture (random init), "
+                "log-mel + encoder + greedy decode, 256 synthetic 30 s clips per GPU"},
+    "small-sweep": {"model": "small", "clips": 64, "sweep": [32, 64, 128, 256, 512], "workload": "BASELINE.json configs[4]: "
+                    "whisper-small architecture (random init), log-mel + encoder + greedy decode, batch sweep per GPU"},
+}
+MODEL = "tiny"          # set from --config in main()
+CLIPS_PER_GPU = 64
+
+# algorithmic work per clip
 MEL_BYTES_PER_CLIP = 480000 * 4 + 80 * 3000 * 4  # 2 880 000 B
-ENC_GEMM_FLOP_PER_CLIP = {"tiny": 4 * (1.769e9 + 3.539e9), "base": 0.0, "small": 0.0}
-ENC_ATTN_FLOP_PER_CLIP = {"tiny": 4 * 3.456e9}
+
+
+def enc_gemm_flop_per_clip(dims):
+    """QKV + out-proj (4 d^2) and the MLP (8 d^2) over 1500 positions, all layers: 2*M*N*K."""
+    d, L = dims.d_model, dims.n_enc_layers
+    return L * (2.0 * 1500 * 4 * d * d + 2.0 * 1500 * 8 * d * d)
+
+
+def enc_attn_flop_per_clip(dims):
+    """QK^T and PV: 4 * S^2 * d per layer."""
+    return dims.n_enc_layers * 4.0 * 1500 * 1500 * dims.d_model
 
 
 def peaks():
@@ -146,12 +170,15 @@ def run_reference(args):
     threads = os.cpu_count() or 1
     dims = synth.DIMS[MODEL]
     W = synth.init_weights(dims, seed=0)
-    n_sample = 2
+    # a bounded sample of the workload: the CPU path runs at ~37 audio-s/s (0.8 s per clip), so a step is 2 clips and the
+    # run is capped at 6 timed steps + 1 warm-up — stated in the line, not applied silently
+    n_sample, steps_cap, warmup_cap = 2, 6, 1
     pcm = synth.synth_pcm(n_sample, seed=0)
-    for _ in range(max(0, min(args.warmup, 1))):
+    warm = max(0, min(args.warmup, warmup_cap))
+    for _ in range(warm):
         cpu_path_seconds(pcm[:1], W, dims, threads)
     tot = 0.0
-    steps = max(1, min(args.steps, 3))
+    steps = max(1, min(args.steps, steps_cap))
     mel_kind = "port"
     for _ in range(steps):
         dt, _, mel_kind = cpu_path_seconds(pcm, W, dims, threads)
@@ -159,12 +186,14 @@ def run_reference(args):
     rtfx = n_sample * CLIP_S * steps / tot
     line = {
         "impl": "reference", "metric": METRIC, "value": rtfx, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
-        "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * tot / steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": warm, "ms_per_step": 1e3 * tot / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "whisper-tiny log-mel + encoder + greedy decode (<=27 new tokens), synthetic 30 s clips, "
+        "config": {"workload": f"whisper-{MODEL} log-mel + encoder + greedy decode (<=27 new tokens), synthetic 30 s clips, "
                                "batch-1 calls like the reference API; TFLite unavailable on this box -> encoder/decoder "
                                "run through the fp32 numpy port with the reference's no-KV-cache loop",
-                   "clips_per_step": n_sample},
+                   "clips_per_step": n_sample, "steps_requested": args.steps, "steps_cap": steps_cap,
+                   "warmup_requested": args.warmup, "warmup_cap": warmup_cap,
+                   "ranks": "rank 0 only (host cores are shared by the ranks of a node)"},
         "cpu_baseline": {"value": rtfx, "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": f"{n_sample} clips x {steps} steps; mel = {mel_kind} log_mel_spectrogram "
                                    f"({threads} threads), encoder/decoder = numpy fp32 port (BLAS threads = all)"},
@@ -177,9 +206,11 @@ def run_reference(args):
 # ----------------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------------
-def run_gpu(args):
+def run_gpu(args, cfg_name, B):
+    """One JSON line for configuration `cfg_name` at B clips per batch and GPU."""
     import torch
     from whisper_tflite_b200 import capi, synth
+    cfg = CONFIGS[cfg_name]
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -190,18 +221,27 @@ def run_gpu(args):
     if world > 1:
         import torch.distributed as dist_mod
         dist = dist_mod
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        if not dist.is_initialized():
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     if rank == 0:
         wpath = ensure_weights(MODEL)
     if dist:
         dist.barrier()
     wpath = ensure_weights(MODEL)
+    dims = synth.DIMS[MODEL]
 
-    B = CLIPS_PER_GPU
     # Serving arrangement (capi.EnginePool): N engines per GPU on separate streams, batches alternate between them, so
-    # one batch's greedy decoder (latency-bound, 4 clusters of 16 clips) runs underneath the next batch's mel + encoder.
+    # one batch's greedy decoder (latency-bound, a few thread-block clusters) runs underneath the next batches' mel +
+    # encoder. Decoder clusters of 8 CTAs (wt_config.decoder_cluster) hold 16 clips on 8 SMs instead of 16: a batch's
+    # decoder takes longer but fewer SM-milliseconds, and five engines keep enough batches in flight.
     n_eng = max(1, args.engines)
-    engs = [capi.Engine(wpath, device=local, max_batch=B, precision=capi.PRECISION_BF16) for _ in range(n_eng)]
+    # activations + cross-K/V streams of one engine (bytes); the pool must fit well inside 180 GB
+    per_engine = B * (1500 * dims.d_model * 2 * 11 + 3002 * (dims.d_model + 80) * 2 + 480000 * 4 + 80 * 3000 * 8 +
+                      dims.n_dec_layers * dims.n_heads * 12 * 2 * 128 * 64 * 2) + 400e6
+    n_eng = max(1, min(n_eng, int(140e9 // per_engine)))
+    dec_cluster = args.dec_cluster if n_eng > 1 else 0
+    engs = [capi.Engine(wpath, device=local, max_batch=B, precision=capi.PRECISION_BF16, decoder_cluster=dec_cluster)
+            for _ in range(n_eng)]
     # dedicated (non-default) streams: the engines enqueue on them and the CUDA events below are recorded on them
     # (wt_set_stream(NULL) would select an engine's own stream, which torch's events cannot see)
     streams = [torch.cuda.Stream() for _ in range(n_eng)]
@@ -212,31 +252,47 @@ def run_gpu(args):
         e.set_stream(st_.cuda_stream)
         e.set_decoder_group(args.dec_group if n_eng > 1 else 0)
     eng = engs[0]
-    # every rank gets its own clips (global clip index = rank*B + i), 3 rotating sets so no step re-reads warm inputs
-    n_sets = 3
-    sets = [synth.synth_pcm(B, seed=1000 * s_ + rank) for s_ in range(n_sets)]
+    if "stream_windows" in cfg:
+        # one hour = 120 windows; the x32 stream's window i is hour[i % 120]; a rank owns a contiguous run of batches.
+        # Batch compositions repeat every lcm(64, 120) / 64 = 15 batches: 15 distinct PCM sets.
+        n_win, rep = cfg["stream_windows"], cfg["repeat"]
+        hour = synth.synth_pcm(n_win, seed=4242)
+        total_batches = n_win * rep // B
+        assert total_batches % world == 0
+        units = total_batches // world                      # batches per step and rank
+        first = rank * units
+        n_sets = 15
+        sets = [np.ascontiguousarray(hour[[(k * B + i) % n_win for i in range(B)]]) for k in range(n_sets)]
+        set_of = lambda k: (first + k) % n_sets             # noqa: E731  batch k of this rank's run
+        audio_s_step = n_win * rep * CLIP_S                 # whole job per step
+        scaling = "strong"
+    else:
+        # every rank gets its own clips (global clip index = rank*B + i), 3 rotating sets so no step re-reads warm inputs
+        n_sets, units = 3, 1
+        sets = [synth.synth_pcm(B, seed=1000 * s_ + rank) for s_ in range(n_sets)]
+        set_of = lambda k: k % n_sets                       # noqa: E731
+        audio_s_step = world * B * CLIP_S
+        scaling = "weak"
     d_sets = [torch.from_numpy(p_).cuda() for p_ in sets]
     h_sets = [torch.from_numpy(p_).pin_memory() for p_ in sets]
-    # one result buffer per timed step (not per engine): every step's ids are compared with a single-engine pass
+    # one result buffer per timed batch (not per engine): every batch's ids are compared with a single-engine pass
     # over the same PCM set after the timed region
-    n_out = max(args.steps, args.warmup * n_eng, n_eng, 3)
+    n_out = max(args.steps * units, args.warmup * n_eng, n_eng, 3)
     d_ids = [torch.empty(B, capi.MAX_TOKENS, dtype=torch.int32, device="cuda") for _ in range(n_out)]
     d_lens = [torch.empty(B, dtype=torch.int32, device="cuda") for _ in range(n_out)]
     h_ids = [torch.empty(B, capi.MAX_TOKENS, dtype=torch.int32).pin_memory() for _ in range(n_out)]
     h_lens = [torch.empty(B, dtype=torch.int32).pin_memory() for _ in range(n_out)]
 
-    def step_dev(i):
-        j = i % n_eng
-        engs[j].transcribe_tokens(d_sets[i % n_sets], ids_out=d_ids[i % n_out], lens_out=d_lens[i % n_out])  # asynchronous enqueue
+    def batch_dev(k):
+        engs[k % n_eng].transcribe_tokens(d_sets[set_of(k)], ids_out=d_ids[k % n_out], lens_out=d_lens[k % n_out])  # asynchronous enqueue
 
-    def step_e2e(i):
-        j = i % n_eng
-        engs[j].transcribe_tokens(h_sets[i % n_sets], ids_out=h_ids[i % n_out], lens_out=h_lens[i % n_out])  # H2D + compute + D2H, returns synced
+    def batch_e2e(k):
+        engs[k % n_eng].transcribe_tokens(h_sets[set_of(k)], ids_out=h_ids[k % n_out], lens_out=h_lens[k % n_out])  # H2D + compute + D2H, returns synced
 
     from concurrent.futures import ThreadPoolExecutor
     workers = [ThreadPoolExecutor(1) for _ in range(n_eng)]  # one host thread per engine (the C call releases the GIL)
 
-    def timed(fn, steps, threaded=False):
+    def timed(fn, n_batches, threaded=False):
         torch.cuda.synchronize()
         if dist:
             dist.barrier()
@@ -246,11 +302,11 @@ def run_gpu(args):
         for st_ in streams[1:]:
             st_.wait_event(a)
         if threaded:
-            for f in [workers[i % n_eng].submit(fn, i) for i in range(steps)]:
+            for f in [workers[k % n_eng].submit(fn, k) for k in range(n_batches)]:
                 f.result()
         else:
-            for i in range(steps):
-                fn(i)
+            for k in range(n_batches):
+                fn(k)
         for st_ in streams[1:]:
             stream.wait_stream(st_)
         b.record(stream)
@@ -263,18 +319,18 @@ def run_gpu(args):
             dist.barrier()
         return ms
 
-    for i in range(args.warmup * n_eng):   # W warm-up steps per engine
-        step_dev(i)
+    for k in range(args.warmup * n_eng):   # W warm-up batches per engine
+        batch_dev(k)
     l0 = sum(e.launch_count for e in engs)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ms = timed(step_dev, args.steps)
+    ms = timed(batch_dev, args.steps * units)
     launches = sum(e.launch_count for e in engs) - l0
     clocks = sampler.stop() if rank == 0 else None
-    for i in range(max(n_eng, min(args.warmup, 2))):
-        step_e2e(i)
-    ms_e2e = timed(step_e2e, args.steps, threaded=n_eng > 1)
+    for k in range(max(n_eng, min(args.warmup, 2))):
+        batch_e2e(k)
+    ms_e2e = timed(batch_e2e, args.steps * units, threaded=n_eng > 1)
 
     # per-stage device times (CUDA events around every launch, same stream) for the roofline
     prof_steps = max(1, min(args.steps, 3))
@@ -282,11 +338,11 @@ def run_gpu(args):
     p_ids = torch.empty(B, capi.MAX_TOKENS, dtype=torch.int32, device="cuda")
     p_lens = torch.empty(B, dtype=torch.int32, device="cuda")
     eng.profile(True)
-    for i in range(prof_steps):   # engine 0 alone, steps back to back: per-kernel durations without co-running kernels
+    for i in range(prof_steps):   # engine 0 alone, batches back to back: per-kernel durations without co-running kernels
         eng.transcribe_tokens(d_sets[i % n_sets], ids_out=p_ids, lens_out=p_lens)
     stages = eng.profile_read()
     eng.profile(False)
-    # result check (outside the timed region): the ids of EVERY timed step, device-resident and end-to-end, against a
+    # result check (outside the timed region): the ids of EVERY timed batch, device-resident and end-to-end, against a
     # single-engine pass over the same PCM set — a window maps to one id list whatever engine, stream or co-running
     # kernels it met (whisper.cpp:367-400); plus the decoded lengths (the loop exits early on EOT, so RTFx depends on them)
     torch.cuda.synchronize()
@@ -298,19 +354,19 @@ def run_gpu(args):
         torch.cuda.synchronize()
         ref.append((ri.cpu(), rl.cpu()))
     mism = 0
-    for i in range(args.steps):
-        ri, rl = ref[i % n_sets]
-        mism += int((d_ids[i % n_out].cpu() != ri).any(dim=1).sum()) + int((h_ids[i % n_out] != ri).any(dim=1).sum())
-        mism += int((d_lens[i % n_out].cpu() != rl).sum()) + int((h_lens[i % n_out] != rl).sum())
+    n_checked = min(args.steps * units, n_out)
+    for k in range(args.steps * units - n_checked, args.steps * units):
+        ri, rl = ref[set_of(k)]
+        mism += int((d_ids[k % n_out].cpu() != ri).any(dim=1).sum()) + int((h_ids[k % n_out] != ri).any(dim=1).sum())
+        mism += int((d_lens[k % n_out].cpu() != rl).sum()) + int((h_lens[k % n_out] != rl).sum())
     all_lens = torch.cat([rl for _, rl in ref]).float()
     lens_ok = bool(((all_lens >= 5) & (all_lens <= capi.MAX_TOKENS)).all().item())
     results_ok = lens_ok and mism == 0
 
     if rank == 0:
         pk = peaks()
-        audio_s = world * B * CLIP_S
-        value = audio_s * args.steps / (ms / 1e3)
-        e2e_value = audio_s * args.steps / (ms_e2e / 1e3)
+        value = audio_s_step * args.steps / (ms / 1e3)
+        e2e_value = audio_s_step * args.steps / (ms_e2e / 1e3)
         per_stage = {k: {"ms_per_step": v[0] / prof_steps, "launches_per_step": v[1] / prof_steps}
                      for k, v in stages.items() if v[1]}
         total_prof = sum(v["ms_per_step"] for v in per_stage.values())
@@ -326,18 +382,17 @@ def run_gpu(args):
                 return {"kernel": "mel_frames_kernel", "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"],
                         "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": None}
             if name == "enc_gemm":
-                ach = B * ENC_GEMM_FLOP_PER_CLIP[MODEL] / sec / 1e12
+                ach = B * enc_gemm_flop_per_clip(dims) / sec / 1e12
                 return {"kernel": "gemm_bf16_sm100_kernel (encoder qkv/out/fc1/fc2)", "bound": "tensor", "achieved": ach,
                         "peak": pk["bf16_sustained"], "unit": "TFLOP/s", "frac": ach / pk["bf16_sustained"],
                         "traffic": None}
             if name == "enc_attention":
-                ach = B * ENC_ATTN_FLOP_PER_CLIP[MODEL] / sec / 1e12
-                return {"kernel": "encoder attention", "bound": "tensor", "achieved": ach, "peak": pk["bf16_sustained"],
+                ach = B * enc_attn_flop_per_clip(dims) / sec / 1e12
+                return {"kernel": "attention3_sm100_kernel", "bound": "tensor", "achieved": ach, "peak": pk["bf16_sustained"],
                         "unit": "TFLOP/s", "frac": ach / pk["bf16_sustained"], "traffic": None}
             if name == "dec_cross_attn":
                 # per launch: K and V of one layer for every clip: B * 2 * 1500 * d * 2 bytes
-                d = synth.DIMS[MODEL].d_model
-                byt = B * 2 * 1500 * d * 2 * st["launches_per_step"]
+                byt = B * 2 * 1500 * dims.d_model * 2 * st["launches_per_step"]
                 ach = byt / sec / 1e9
                 return {"kernel": "decode_cross_attn_kernel", "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"],
                         "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": None}
@@ -345,8 +400,7 @@ def run_gpu(args):
                 # one launch = the whole greedy loop: per position, every layer streams each clip's cross K/V
                 # (B * 2 * 1500 * d bf16) and the layer's projection weights (14 d^2 bf16) once; the tied logits matrix
                 # (V * d bf16) once per generated token
-                dm = synth.DIMS[MODEL]
-                d, L, V = dm.d_model, dm.n_dec_layers, dm.n_vocab
+                d, L, V = dims.d_model, dims.n_dec_layers, dims.n_vocab
                 n_pos, n_gen = capi.MAX_TOKENS - 1, capi.MAX_TOKENS - len(capi.REFERENCE_PROMPT)
                 byt = (n_pos * L * (B * 2 * 1500 * d * 2 + 14 * d * d * 2) + n_gen * V * d * 2) * st["launches_per_step"]
                 ach = byt / sec / 1e9
@@ -356,84 +410,99 @@ def run_gpu(args):
 
         roofs = {k: roof(k) for k in ("mel_frames", "enc_gemm", "enc_attention", "dec_cross_attn", "dec_persistent")}
         # traffic: DRAM bytes per launch from the committed `ncu --set full` capture of the same workload
-        # (profiles/traffic.json, written by tools/ncu_summary.py); single-kernel stages only
-        try:
-            tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["bytes_per_launch"]
-            for stage_name, kern in (("mel_frames", "mel_frames_kernel"), ("dec_persistent", "decoder_stream_kernel")):
-                if roofs.get(stage_name) and tr.get(kern):
-                    roofs[stage_name]["traffic"] = tr[kern][0]
-        except (OSError, KeyError, ValueError):
-            pass
+        # (profiles/traffic.json, written by tools/ncu_summary.py); single-kernel stages of the headline config only
+        if cfg_name == "tiny64":
+            try:
+                tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["bytes_per_launch"]
+                for stage_name, kern in (("mel_frames", "mel_frames_kernel"), ("dec_persistent", "decoder_stream_kernel")):
+                    if roofs.get(stage_name) and tr.get(kern):
+                        roofs[stage_name]["traffic"] = tr[kern][0]
+            except (OSError, KeyError, ValueError):
+                pass
         roofline = roofs.get(dom) or roofs["enc_gemm"] or {}
         roofline = dict(roofline)
         roofline["dominant_stage"] = dom
         roofline["peak_source"] = pk["src"] + " (sustained figure: kernels timed inside a long step)"
         roofline["all"] = {k: v for k, v in roofs.items() if v}
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "metric": METRIC if cfg_name == "tiny64" else f"RTFx (audio-sec/sec) {cfg_name}", "value": value, "unit": UNIT,
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": "BASELINE.json configs[1]: whisper-tiny (multilingual vocab 51865, language tag de) "
-                                   "log-mel + encoder + greedy decode (4 prompt + <=27 new tokens), 64 synthetic 30 s "
-                                   "clips per GPU, seeded random-init weights",
-                       "clips_per_gpu": B, "audio_seconds_per_step": audio_s, "parallelism": f"clip-sharded x{world}, "
-                       "no data-path collective",
-                       "pipeline": (f"{n_eng} engines per GPU on separate streams, batches alternate between them (batch i's "
-                                    "decoder overlaps batch i+1's mel + encoder); decoder %d clips per cluster" % args.dec_group
-                                    if n_eng > 1 else "1 engine, steps back to back"),
-                       "l2": "no explicit flush: three rotating 123 MB PCM sets and >1 GB of activations per step "
+            "config": {"name": cfg_name, "workload": cfg["workload"],
+                       "clips_per_batch": B, "batches_per_step_per_gpu": units, "audio_seconds_per_step": audio_s_step,
+                       "parallelism": f"clip-sharded x{world}, no data-path collective",
+                       "pipeline": (f"{n_eng} engines per GPU on separate streams, batches alternate between them (a batch's "
+                                    f"decoder overlaps the next batches' mel + encoder); decoder clusters of {dec_cluster or 16} CTAs, "
+                                    f"{args.dec_group} clips each" if n_eng > 1 else "1 engine, batches back to back"),
+                       "l2": "no explicit flush: rotating PCM sets of 123 MB+ and >1 GB of activations per batch "
                              "exceed the 126 MB L2"},
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
-                    "h2d_bytes_per_step": int(world * B * 480000 * 4),
-                    "d2h_bytes_per_step": int(world * B * (capi.MAX_TOKENS + 1) * 4)},
+                    "h2d_bytes_per_step": int(world * units * B * 480000 * 4),
+                    "d2h_bytes_per_step": int(world * units * B * (capi.MAX_TOKENS + 1) * 4)},
             "roofline": roofline,
             "stages_ms_per_step": {k: round(v["ms_per_step"], 4) for k, v in per_stage.items()},
             "stages_total_ms": round(total_prof, 3), "results_ok": results_ok,
-            "results_check": {"what": "ids and lens of every timed step (device-resident and e2e) == single-engine pass over the same PCM set",
-                              "clips_differing": mism, "steps_checked": 2 * args.steps,
+            "results_check": {"what": "ids and lens of every timed batch (device-resident and e2e) == single-engine pass over the same PCM set",
+                              "clips_differing": mism, "batches_checked": 2 * n_checked,
                               "tokens_per_clip": {"mean": float(all_lens.mean()), "min": int(all_lens.min()), "max": int(all_lens.max())}},
         }
         if world == 1 and not args.no_cpu_baseline:
             from oracle import mel as omel
             omel.build()
-            dims = synth.DIMS[MODEL]
             W = synth.init_weights(dims, seed=0)
             threads = os.cpu_count() or 1
-            n_sample = 3
+            n_sample = 3 if MODEL == "tiny" else 2 if MODEL == "base" else 1
             dt, t_mel, mel_kind = cpu_path_seconds(sets[0][:n_sample], W, dims, threads)
             line["cpu_baseline"] = {
                 "value": n_sample * CLIP_S / dt, "unit": UNIT, "cores": threads, "kind": "port",
-                "sample": f"{n_sample} of the step's 64 clips, batch-1 calls: {mel_kind} log_mel_spectrogram "
+                "sample": f"{n_sample} of the batch's {B} clips, batch-1 calls: {mel_kind} log_mel_spectrogram "
                           f"({threads} threads, {1e3 * t_mel / n_sample:.1f} ms/clip) + fp32 numpy port of the "
                           "encoder/decoder graphs with the reference's no-KV-cache loop (TFLite unavailable on this box)"}
-        print(json.dumps(line))
-    if dist:
-        dist.destroy_process_group()
+        print(json.dumps(line), flush=True)
+    for e in engs:
+        e.close()
+    for w_ in workers:
+        w_.shutdown(wait=True)
     return 0
 
 
 def main():
+    global MODEL, CLIPS_PER_GPU
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="tiny64", choices=sorted(CONFIGS),
+                    help="BASELINE.json configuration (default: configs[1], the one the metric is quoted on)")
+    ap.add_argument("--clips", type=int, default=0, help="clips per batch and GPU (0 = the configuration's)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--dec-group", type=int, default=16,
-                    help="clips per decoder cluster when engines > 1 (64 clips: 16 -> 4 clusters = 64 SMs, 13 -> 5 = 80 SMs)")
-    ap.add_argument("--engines", type=int, default=3, help="engines per GPU that batches alternate between (1 = no pipelining)")
+    ap.add_argument("--dec-group", type=int, default=16, help="clips per decoder cluster when engines > 1")
+    ap.add_argument("--dec-cluster", type=int, default=8,
+                    help="CTAs per decoder cluster when engines > 1 (8: 16 clips on 8 SMs; 16: lowest latency per batch)")
+    ap.add_argument("--engines", type=int, default=5, help="engines per GPU that batches alternate between (1 = no pipelining)")
     args = ap.parse_args()
+    cfg = CONFIGS[args.config]
+    MODEL = cfg["model"]
+    CLIPS_PER_GPU = args.clips or cfg["clips"]
     if args.impl == "reference":
         return run_reference(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.gpus > 1 and world == 1:
         # convenience: re-launch under torchrun when called directly with --gpus N
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
-               "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__), "--gpus", str(args.gpus),
-               "--steps", str(args.steps), "--warmup", str(args.warmup)]
+               "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__)] + sys.argv[1:]
         return subprocess.call(cmd)
-    return run_gpu(args)
+    rc = 0
+    for B in (cfg.get("sweep") if "sweep" in cfg and not args.clips else [CLIPS_PER_GPU]):
+        rc |= run_gpu(args, args.config, B)
+    if world > 1:
+        import torch.distributed as dist
+        if dist.is_initialized():
+            dist.destroy_process_group()
+    return rc
 
 
 if __name__ == "__main__":

@@ -58,6 +58,8 @@ typedef struct wt_config {
   int32_t precision;   /* wt_precision */
   int32_t max_batch;   /* clips per call the engine is sized for (>= 1) */
   int32_t keep_logits; /* != 0: keep the f32 logits of every decode step (debug/parity; costs B*27*V*4 bytes) */
+  int32_t decoder_cluster; /* CTAs per decoder cluster: 0 = default (16: lowest latency of a single call), 8 or 4 = fewer SMs
+                              per batch (a pool of engines keeps more batches in flight: highest throughput per GPU) */
 } wt_config;
 
 typedef struct wt_dims {

@@ -36,7 +36,7 @@ EXPORTED = [
 
 class WtConfig(ctypes.Structure):
     _fields_ = [("struct_size", ctypes.c_int32), ("precision", ctypes.c_int32), ("max_batch", ctypes.c_int32),
-                ("keep_logits", ctypes.c_int32)]
+                ("keep_logits", ctypes.c_int32), ("decoder_cluster", ctypes.c_int32)]
 
 
 class WtDims(ctypes.Structure):
@@ -96,9 +96,10 @@ class Engine:
     """One engine per device; not re-entrant (same contract as the reference's Engine)."""
 
     def __init__(self, weights_path: Optional[str], device: int = 0, max_batch: int = 1,
-                 precision: int = PRECISION_BF16, keep_logits: bool = False, filters: Optional[np.ndarray] = None):
+                 precision: int = PRECISION_BF16, keep_logits: bool = False, filters: Optional[np.ndarray] = None,
+                 decoder_cluster: int = 0):
         self.lib = load_library()
-        cfg = WtConfig(ctypes.sizeof(WtConfig), precision, max_batch, int(keep_logits))
+        cfg = WtConfig(ctypes.sizeof(WtConfig), precision, max_batch, int(keep_logits), int(decoder_cluster))
         h = ctypes.c_void_p()
         _check(self.lib.wt_engine_create(ctypes.byref(cfg), weights_path.encode() if weights_path else None,
                                          int(device), ctypes.byref(h)))
@@ -293,9 +294,10 @@ class EnginePool:
     the H2D copy of a batch also overlaps the other engine's compute."""
 
     def __init__(self, weights_path: str, n_engines: int = 2, device: int = 0, max_batch: int = 64,
-                 precision: int = PRECISION_BF16, decoder_group: int = 16):
+                 precision: int = PRECISION_BF16, decoder_group: int = 16, decoder_cluster: int = 0):
         from concurrent.futures import ThreadPoolExecutor
-        self.engines = [Engine(weights_path, device=device, max_batch=max_batch, precision=precision)
+        self.engines = [Engine(weights_path, device=device, max_batch=max_batch, precision=precision,
+                               decoder_cluster=decoder_cluster if n_engines > 1 else 0)
                         for _ in range(n_engines)]
         for e in self.engines:
             e.set_decoder_group(decoder_group if n_engines > 1 else 0)

@@ -274,6 +274,7 @@ struct wt_engine {
   bool dec_persistent = false;
   int dec_cluster = 0, dec_group = 0, dec_groups_cap = 0, dec_active_clusters = 0;
   int dec_group_user = 0;  // wt_set_decoder_group (0 = automatic)
+  int dec_cluster_cfg = 0; // wt_config.decoder_cluster (0 = default)
   int attn_kernel = 3;      // encoder attention: 3 = attn3_sm100.cuh (default), 2 = attn2_sm100.cuh (WT_ATTN=2)
   unsigned long long* d_hash = nullptr;   // wt_debug_hash accumulator
   int* gemm_sched = nullptr;  // {next tile, CTAs done} of the GEMM kernel's dynamic tile scheduler (self-resetting)
@@ -811,6 +812,11 @@ int wt_engine::init_persistent_decoder() {
   dec_cluster = 0;
   const int want[2] = {16, 8};
   const char* ocl = getenv("WT_DEC_CLUSTER");
+  char ocl_buf[16];
+  if (!ocl && dec_cluster_cfg > 0) {   // wt_config.decoder_cluster
+    snprintf(ocl_buf, sizeof(ocl_buf), "%d", dec_cluster_cfg);
+    ocl = ocl_buf;
+  }
   for (int i = 0; i < 2 && !dec_cluster; ++i) {
     const int cs = ocl ? atoi(ocl) : want[i];
     if (cs < 1 || cs > wt::kDecMaxCluster) return fail(WT_ERR_INVALID, "WT_DEC_CLUSTER must be in [1, %d]", wt::kDecMaxCluster);
@@ -1269,6 +1275,7 @@ int wt_engine_create(const wt_config* cfg, const char* weights_path, int device,
   if (!cfg || cfg->struct_size != (int32_t)sizeof(wt_config)) return fail(WT_ERR_INVALID, "wt_config.struct_size mismatch");
   if (cfg->max_batch < 1 || cfg->max_batch > 4096) return fail(WT_ERR_INVALID, "max_batch outside [1, 4096]");
   if (cfg->precision != WT_PRECISION_BF16 && cfg->precision != WT_PRECISION_FP32_VERIFY) return fail(WT_ERR_INVALID, "unknown precision");
+  if (cfg->decoder_cluster < 0 || cfg->decoder_cluster > 16) return fail(WT_ERR_INVALID, "decoder_cluster outside [0, 16]");
   int n_dev = 0;
   if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev < 1) return fail(WT_ERR_CUDA, "no CUDA device visible: this library has no CPU path");
   if (device < 0 || device >= n_dev) return fail(WT_ERR_INVALID, "device %d outside [0, %d)", device, n_dev);
@@ -1281,6 +1288,7 @@ int wt_engine_create(const wt_config* cfg, const char* weights_path, int device,
   e->precision = cfg->precision;
   e->max_batch = cfg->max_batch;
   e->keep_logits = cfg->keep_logits;
+  e->dec_cluster_cfg = cfg->decoder_cluster;
   e->num_sms = prop.multiProcessorCount;
   int st = WT_OK;
   if (cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking) != cudaSuccess) st = fail(WT_ERR_CUDA, "cudaStreamCreate failed");
