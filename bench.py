@@ -404,8 +404,16 @@ def run_gpu(args, cfg_name, B):
                 n_pos, n_gen = capi.MAX_TOKENS - 1, capi.MAX_TOKENS - len(capi.REFERENCE_PROMPT)
                 byt = (n_pos * L * (B * 2 * 1500 * d * 2 + 14 * d * d * 2) + n_gen * V * d * 2) * st["launches_per_step"]
                 ach = byt / sec / 1e9
-                return {"kernel": "decoder_stream_kernel (persistent greedy loop)", "bound": "hbm", "achieved": ach,
-                        "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": None}
+                # the launch occupies n_clusters x cluster CTAs = that many SMs by design (the rest of the chip runs the
+                # other engines' encoders): frac is against the WHOLE chip's HBM peak, frac_of_sm_share against the
+                # share of it that the launch's SMs would get (148 SMs)
+                n_sms = ((B + args.dec_group - 1) // args.dec_group) * (dec_cluster or 16) if n_eng > 1 else None
+                r = {"kernel": "decoder_stream_kernel (persistent greedy loop)", "bound": "hbm", "achieved": ach,
+                     "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": None}
+                if n_sms:
+                    r["sms_used"] = n_sms
+                    r["frac_of_sm_share"] = ach / (pk["hbm_gbs"] * min(n_sms, 148) / 148.0)
+                return r
             return None
 
         roofs = {k: roof(k) for k in ("mel_frames", "enc_gemm", "enc_attention", "dec_cross_attn", "dec_persistent")}

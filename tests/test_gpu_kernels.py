@@ -1,7 +1,7 @@
 """Kernel-level parity of the production tcgen05 kernels against plain PyTorch fp32 references of the same
 (bf16-rounded) operands, through the C ABI's debug entries (wt_debug_attention_bf16, wt_debug_gemm_ex):
 
-  * attention2_sm100_kernel for S in {92, 128, 129, 1500} (masked last key block; 1500 = 11*128 + 92), and a row whose
+  * attention3_sm100_kernel for S in {92, 128, 129, 1500} (masked last key block; 1500 = 11*128 + 92), and a row whose
     score jumps by more than 2^64 against everything seen before (the redo branch of the streamed reference maximum);
   * gemm_bf16_sm100_kernel's addressing / epilogues the plain GEMM test does not reach: the residual add IN PLACE,
     the 3-tap convolution addressing (against torch.conv1d, strides 1 and 2), the cross-K/V scatter into the decoder's
@@ -27,7 +27,7 @@ def _attn_ref(qkv, H):
 
 
 @pytest.mark.parametrize("S", [92, 128, 129, 1500])
-def test_attention2_vs_torch(S):
+def test_attention_vs_torch(S):
     import torch
     from whisper_tflite_b200 import capi
     H, B = 2, 2
@@ -44,10 +44,10 @@ def test_attention2_vs_torch(S):
     assert err <= 1.5e-2 * ref.abs().max().item(), (S, err, ref.abs().max().item())
 
 
-def test_attention2_score_jump_redo_branch():
+def test_attention_score_jump_redo_branch():
     """Keys of the first blocks score ~0 for query row 5; key 700 (block 5) scores 8*8*64*0.125 = 512 natural-log units
     = 739 in the exp2 domain: more than 64 above the running reference, so the block is redone with its exact maximum
-    (attn2_sm100.cuh). The softmax of that row is one-hot on key 700; every other row is ordinary."""
+    (attn3_sm100.cuh). The softmax of that row is one-hot on key 700; every other row is ordinary."""
     import torch
     from whisper_tflite_b200 import capi
     H, B, S = 1, 1, 1500

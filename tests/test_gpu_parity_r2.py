@@ -1,4 +1,4 @@
-"""Round-2 parity gates for the PRODUCTION bf16 kernels (gemm_bf16_sm100_kernel, attention2_sm100_kernel,
+"""Round-2 parity gates for the PRODUCTION bf16 kernels (gemm_bf16_sm100_kernel, attention3_sm100_kernel,
 decoder_stream_kernel), through the C ABI:
 
   * bitwise reproducibility of one tiny/64 batch repeated >= 200 times on a three-engine pool (ids AND digests of the

@@ -15,7 +15,9 @@ n = int(sys.argv[1]) if len(sys.argv) > 1 else 2
 size = sys.argv[2] if len(sys.argv) > 2 else "tiny"
 B = int(sys.argv[3]) if len(sys.argv) > 3 else 64
 bench.MODEL = size
-eng = capi.Engine(bench.ensure_weights(size), max_batch=B)
+# the bench's arrangement: decoder clusters of 8 CTAs x 16 clips (ONE_STEP_CLUSTER / ONE_STEP_GROUP override)
+eng = capi.Engine(bench.ensure_weights(size), max_batch=B, decoder_cluster=int(os.environ.get("ONE_STEP_CLUSTER", "8")))
+eng.set_decoder_group(int(os.environ.get("ONE_STEP_GROUP", "16")))
 init_launches = eng.launch_count
 pcm = torch.from_numpy(synth.synth_pcm(B, seed=0)).cuda()
 ids = torch.empty(B, 31, dtype=torch.int32, device="cuda")

@@ -275,7 +275,6 @@ struct wt_engine {
   int dec_cluster = 0, dec_group = 0, dec_groups_cap = 0, dec_active_clusters = 0;
   int dec_group_user = 0;  // wt_set_decoder_group (0 = automatic)
   int dec_cluster_cfg = 0; // wt_config.decoder_cluster (0 = default)
-  int attn_kernel = 3;      // encoder attention: 3 = attn3_sm100.cuh (default), 2 = attn2_sm100.cuh (WT_ATTN=2)
   unsigned long long* d_hash = nullptr;   // wt_debug_hash accumulator
   int* gemm_sched = nullptr;  // {next tile, CTAs done} of the GEMM kernel's dynamic tile scheduler (self-resetting)
   float* pd_qs = nullptr;
@@ -505,10 +504,6 @@ int wt_engine::attention_bf16(const void* qkv_, void* out, int n_clips, int S, i
   WT_TRY(get_map(&mq, qkv_, 3, qd, qs, qbox));
   stage = ST_ENC_ATTN;
   pre_launch();
-  if (attn_kernel == 2) {
-    wt::attention2_sm100_kernel<<<dim3((S + 127) / 128, H, n_clips), wt::kAt2Threads, wt::Attn2Smem::kTotal, stream>>>(mq, (bf16*)out, S, H);
-    return check_launch("attention2_sm100_kernel");
-  }
   wt::attention3_sm100_kernel<<<dim3((S + 255) / 256, H, n_clips), wt::kAt3Threads, wt::Attn3Smem::kTotal, stream>>>(mq, (bf16*)out, S, H);
   return check_launch("attention3_sm100_kernel");
 }
@@ -554,12 +549,7 @@ int wt_engine::init_kernels() {
   WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<128>::kTotal));
   WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<192>::kTotal));
   WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<256>::kTotal));
-  WT_CUDA_OK(cudaFuncSetAttribute(wt::attention2_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::Attn2Smem::kTotal));
   WT_CUDA_OK(cudaFuncSetAttribute(wt::attention3_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::Attn3Smem::kTotal));
-  {
-    const char* v = getenv("WT_ATTN");   // read once, here: "2" keeps round 1's two-CTAs-per-SM kernel (A/B measurements)
-    attn_kernel = (v && strcmp(v, "2") == 0) ? 2 : 3;
-  }
   WT_TRY(alloc(&gemm_sched, 2, true));   // cudaMemset here; wt_engine_create synchronises the device before returning
   return WT_OK;
 }
