@@ -401,6 +401,30 @@ static int launch_gemm_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMap
   return e->check_launch("gemm_bf16_sm100_kernel");
 }
 
+// CTA-pair kernel (gemm2_bf16_sm100_kernel): 256-row tiles on a cluster of two CTAs
+template <int BN>
+static int launch_gemm2_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMap& mw, wt::GemmBf16Params& p) {
+  using S = wt::Gemm2Smem<BN>;
+  p.n_tiles_n = (p.N + BN - 1) / BN;
+  const int n_tiles = p.tiles_per_batch * p.n_batches * p.n_tiles_n;
+  const int max_pairs = e->num_sms / 2;
+  const int pairs = n_tiles < max_pairs ? n_tiles : max_pairs;
+  if (!e->gemm_sched) return fail(WT_ERR_STATE, "GEMM tile scheduler not allocated (engine not initialised)");
+  p.sched = e->gemm_sched;
+  e->pre_launch();
+  wt::gemm2_bf16_sm100_kernel<BN><<<2 * pairs, wt::kGemmThreads, S::kTotal, e->stream>>>(ma, mw, p);
+  return e->check_launch("gemm2_bf16_sm100_kernel");
+}
+// Where the pair wins (tools/gemm_bench.py, M = 96 000): K >= 768 — fc2 at K = 1536 / 2048 / 3072: 119 -> 111, 193 -> 152,
+// 391 -> 341 us (1.33 PF/s = 0.97 of the sustained cuBLAS figure), QKV at K = 768: 298 -> 285. At K <= 512 a tile is
+// <= 8 k-blocks and the epilogue, not the operand traffic, paces the kernel: the one-CTA kernel is 3-8 % faster there.
+static bool gemm_pair_wanted(int rows_per_batch, int n_batches, int K_total) {
+  static const char* ov = getenv("WT_GEMM_PAIR");   // "0" = never, "1" = whenever the shape allows (A/B measurements)
+  if (ov && ov[0] == '0') return false;
+  const bool fits = (long long)rows_per_batch * n_batches >= 4096 && rows_per_batch >= 256;
+  return fits && ((ov && ov[0] == '1') || K_total >= 768);
+}
+
 static int pick_bn(int M, int N) {
   if (M <= 128) return N >= 16384 ? 128 : 64;
   const int cands[3] = {256, 192, 128};
@@ -415,12 +439,13 @@ int wt_engine::gemm_bf16(const void* A, const uint64_t* a_dims, const uint64_t* 
                          unsigned long long* amax, int force_bn) {
   const int M = rows_per_batch * n_batches;
   const int bn = force_bn ? force_bn : pick_bn(M, L.N);
+  const bool pair = !force_bn && bn >= 128 && gemm_pair_wanted(rows_per_batch, n_batches, K_total);
   CUtensorMap ma, mw;
   const uint32_t abox[3] = {64, 128, 1};
   WT_TRY(get_map(&ma, A, 3, a_dims, a_strides, abox));
   const uint64_t wdims[2] = {(uint64_t)K_total, (uint64_t)L.N};
   const uint64_t wstr[1] = {(uint64_t)K_total * 2};
-  const uint32_t wbox[2] = {64, (uint32_t)bn};
+  const uint32_t wbox[2] = {64, (uint32_t)(pair ? bn / 2 : bn)};   // a CTA of a pair loads its half of the W tile
   WT_TRY(get_map(&mw, L.w, 2, wdims, wstr, wbox));
   wt::GemmBf16Params p{};
   p.bias = L.b;
@@ -452,6 +477,14 @@ int wt_engine::gemm_bf16(const void* A, const uint64_t* a_dims, const uint64_t* 
   for (int i = 0; i < 3; ++i) {
     p.tap_c0[i] = (i < taps && tap_c0) ? tap_c0[i] : 0;
     p.tap_row[i] = (i < taps && tap_row) ? tap_row[i] : 0;
+  }
+  if (pair) {
+    p.tiles_per_batch = (rows_per_batch + 255) / 256;
+    switch (bn) {
+      case 128: return launch_gemm2_bn<128>(this, ma, mw, p);
+      case 192: return launch_gemm2_bn<192>(this, ma, mw, p);
+      case 256: return launch_gemm2_bn<256>(this, ma, mw, p);
+    }
   }
   switch (bn) {
     case 64: return launch_gemm_bn<64>(this, ma, mw, p);
@@ -549,6 +582,9 @@ int wt_engine::init_kernels() {
   WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<128>::kTotal));
   WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<192>::kTotal));
   WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<256>::kTotal));
+  WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm2_bf16_sm100_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::Gemm2Smem<128>::kTotal));
+  WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm2_bf16_sm100_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::Gemm2Smem<192>::kTotal));
+  WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm2_bf16_sm100_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::Gemm2Smem<256>::kTotal));
   WT_CUDA_OK(cudaFuncSetAttribute(wt::attention3_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::Attn3Smem::kTotal));
   WT_TRY(alloc(&gemm_sched, 2, true));   // cudaMemset here; wt_engine_create synchronises the device before returning
   return WT_OK;

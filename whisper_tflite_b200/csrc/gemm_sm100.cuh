@@ -224,6 +224,164 @@ struct GemmSmem {
   static constexpr int kTmemCols = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
 };
 
+// The epilogue of one 128 x BN accumulator tile for one warp (its 32 rows = its TMEM lane quarter): tcgen05.ld in
+// 32-column chunks -> + bias -> GELU -> + addend -> bf16 (or f32) -> transpose through the warp's scratch -> 16-byte
+// coalesced stores through the RowMap, or the K/V-stream scatter, or the fused (max, last index). Returns the row's
+// packed winner (EPI_ARGMAX). Shared by the one-CTA and the CTA-pair kernels.
+template <int BN, int kScrRow>
+__device__ __forceinline__ unsigned long long gemm_epilogue_tile(const GemmBf16Params& p, uint32_t t_row, const float* bias_s,
+                                                                  uint8_t* scr, int lane, int lane_q, int batch, int row0,
+                                                                  int n0) {
+  const int r_in_tile = lane_q * 32 + lane;           // accumulator row owned by this thread
+  const int r_batch = row0 + r_in_tile;               // row within the clip
+  const bool row_ok = r_batch < p.rows_per_batch;
+  unsigned long long best = 0ull;
+  // a tile never straddles a batch: one RowMap division per tile, rows are then row_stride apart
+  const long long c_base = p.cmap.at(batch * p.rows_per_batch + row0);
+  const long long a_base = (p.flags & EPI_ADD) ? p.add_map.at(batch * p.rows_per_batch + row0) : 0ll;
+
+  for (int c0 = 0; c0 < BN; c0 += 32) {
+    // the addend's 32 rows x 32 cols of this warp (coalesced 16-byte pieces) are requested first: their global
+    // latency runs underneath the TMEM load and the bias / GELU math
+    uint4 addv[4];
+    if (p.flags & EPI_ADD) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int piece = i * 32 + lane;          // 128 pieces of 8 bf16: 4 per row
+        const int rr = piece >> 2, pc = piece & 3;
+        const int rb = row0 + lane_q * 32 + rr;
+        const int col = n0 + c0 + pc * 8;
+        addv[i] = make_uint4(0u, 0u, 0u, 0u);
+        if (rb < p.rows_per_batch && col < p.N)
+          addv[i] = *reinterpret_cast<const uint4*>(p.addend + a_base + (long long)(rb - row0) * p.add_map.row_stride + col);
+      }
+    }
+    uint32_t v[32];
+    tmem_ld32(t_row + c0, v);
+    tmem_ld_wait();
+    float f[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+    if (p.flags & EPI_BIAS) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        const float4 b4 = *reinterpret_cast<const float4*>(bias_s + c0 + j);
+        f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
+      }
+    }
+    if (p.flags & EPI_GELU) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = gelu_tanh_fit(f[j]);
+    }
+    if (p.flags & EPI_ADD) {
+      // coalesced fetch of this warp's 32 rows x 32 cols of the addend through the scratch
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int piece = i * 32 + lane;
+        const int rr = piece >> 2, pc = piece & 3;
+        *reinterpret_cast<uint4*>(scr + rr * kScrRow + pc * 16) = addv[i];
+      }
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint4 val = *reinterpret_cast<const uint4*>(scr + lane * kScrRow + i * 16);
+        const uint32_t w[4] = {val.x, val.y, val.z, val.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          f[i * 8 + 2 * j] += __uint_as_float(w[j] << 16);
+          f[i * 8 + 2 * j + 1] += __uint_as_float(w[j] & 0xffff0000u);
+        }
+      }
+      __syncwarp();
+    }
+    if (p.flags & EPI_ARGMAX) {
+      if (row_ok) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int n = n0 + c0 + j;
+          if (n < p.N) best = u64_max(best, pack_val_idx(f[j], (unsigned)n));
+        }
+      }
+    }
+    if (p.flags & EPI_OUT_F32) {
+      // f32 output: 32 cols = 128 bytes per row
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        *reinterpret_cast<float4*>(scr + lane * kScrRow + i * 16) =
+            make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int piece = i * 32 + lane;  // 256 pieces of 4 f32: 8 per row
+        const int rr = piece >> 3, pc = piece & 7;
+        const int rb = row0 + lane_q * 32 + rr;
+        const int col = n0 + c0 + pc * 4;
+        if (rb < p.rows_per_batch && col < p.N) {
+          const float4 val = *reinterpret_cast<const float4*>(scr + rr * kScrRow + pc * 16);
+          float* dst = reinterpret_cast<float*>(p.C) + c_base + (long long)(rb - row0) * p.cmap.row_stride + col;
+          if (col + 3 < p.N && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+            *reinterpret_cast<float4*>(dst) = val;
+          } else {
+            const float tmp[4] = {val.x, val.y, val.z, val.w};
+            for (int q = 0; q < 4; ++q)
+              if (col + q < p.N) dst[q] = tmp[q];
+          }
+        }
+      }
+      __syncwarp();
+    } else if (p.C != nullptr || (p.flags & EPI_SPLIT_KV)) {
+      // bf16 output: 32 cols = 64 bytes per row
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<uint4*>(scr + lane * kScrRow + i * 16) =
+            make_uint4(pack_bf16x2(f[8 * i], f[8 * i + 1]), pack_bf16x2(f[8 * i + 2], f[8 * i + 3]),
+                       pack_bf16x2(f[8 * i + 4], f[8 * i + 5]), pack_bf16x2(f[8 * i + 6], f[8 * i + 7]));
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int piece = i * 32 + lane;
+        const int rr = piece >> 2, pc = piece & 3;
+        const int rb = row0 + lane_q * 32 + rr;
+        const int col = n0 + c0 + pc * 8;
+        if (rb < p.rows_per_batch && col < p.N) {
+          const uint4 val = *reinterpret_cast<const uint4*>(scr + rr * kScrRow + pc * 16);
+          if (p.flags & EPI_SPLIT_KV) {
+            int clip = batch, sq = rb;     // launched per clip (rows_per_batch == kv_S): no division
+            if (p.rows_per_batch != p.kv_S) {
+              const int mm = batch * p.rows_per_batch + rb;
+              clip = mm / p.kv_S;
+              sq = mm - clip * p.kv_S;
+            }
+            const int dm = p.kv_H * 64;
+            const int which = col >= dm, cc = which ? col - dm : col;
+            __nv_bfloat16* dst;
+            if (p.kv_chunk > 0) {
+              int ch = sq >> 7, kin = sq & 127;
+              if (p.kv_chunk != 128) {
+                ch = sq / p.kv_chunk;
+                kin = sq - ch * p.kv_chunk;
+              }
+              // 16-byte segments of a key's 128-byte row are XOR-swizzled by key & 7: the decoder reads the chunk
+              // with ldmatrix straight out of the bulk-copied stage (decoder_stream_sm100.cuh: ds_cross_attn)
+              dst = p.kv_k + ((((size_t)(clip * p.kv_H + (cc >> 6)) * p.kv_cpp + ch) * 2 + which) * p.kv_chunk + kin) * 64 +
+                    (((((cc & 63) >> 3) ^ (kin & 7)) << 3));
+            } else {
+              dst = (which ? p.kv_v : p.kv_k) + (((size_t)(clip * p.kv_H + (cc >> 6)) * p.kv_S + sq) * 64 + (cc & 63));
+            }
+            *reinterpret_cast<uint4*>(dst) = val;
+          } else {
+            *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C) + c_base +
+                                      (long long)(rb - row0) * p.cmap.row_stride + col) = val;
+          }
+        }
+      }
+      __syncwarp();
+    }
+  }
+  return best;
+}
+
 template <int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
@@ -376,160 +534,16 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
       asm volatile("bar.sync %0, 128;" ::"r"(1 + eg) : "memory");
       mbar_wait(bar_tfull + acc, acc_phase);
       tc_fence_after();
-      const int r_in_tile = lane_q * 32 + lane;           // accumulator row owned by this thread
-      const int r_batch = row0 + r_in_tile;               // row within the clip
-      const bool row_ok = r_batch < p.rows_per_batch;
-      const int m = batch * p.rows_per_batch + r_batch;   // logical GEMM row
       const uint32_t t_row = tmem_base + ((uint32_t)(lane_q * 32) << 16) + acc * BN;
-      unsigned long long best = 0ull;
-      // a tile never straddles a batch: one RowMap division per tile, rows are then row_stride apart
-      const long long c_base = p.cmap.at(batch * p.rows_per_batch + row0);
-      const long long a_base = (p.flags & EPI_ADD) ? p.add_map.at(batch * p.rows_per_batch + row0) : 0ll;
-
-      for (int c0 = 0; c0 < BN; c0 += 32) {
-        // the addend's 32 rows x 32 cols of this warp (coalesced 16-byte pieces) are requested first: their global
-        // latency runs underneath the TMEM load and the bias / GELU math
-        uint4 addv[4];
-        if (p.flags & EPI_ADD) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int piece = i * 32 + lane;          // 128 pieces of 8 bf16: 4 per row
-            const int rr = piece >> 2, pc = piece & 3;
-            const int rb = row0 + lane_q * 32 + rr;
-            const int col = n0 + c0 + pc * 8;
-            addv[i] = make_uint4(0u, 0u, 0u, 0u);
-            if (rb < p.rows_per_batch && col < p.N)
-              addv[i] = *reinterpret_cast<const uint4*>(p.addend + a_base + (long long)(rb - row0) * p.add_map.row_stride + col);
-          }
-        }
-        uint32_t v[32];
-        tmem_ld32(t_row + c0, v);
-        tmem_ld_wait();
-        float f[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-        if (p.flags & EPI_BIAS) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 b4 = *reinterpret_cast<const float4*>(bias_s + c0 + j);
-            f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
-          }
-        }
-        if (p.flags & EPI_GELU) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = gelu_tanh_fit(f[j]);
-        }
-        if (p.flags & EPI_ADD) {
-          // coalesced fetch of this warp's 32 rows x 32 cols of the addend through the scratch
-          __syncwarp();
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int piece = i * 32 + lane;
-            const int rr = piece >> 2, pc = piece & 3;
-            *reinterpret_cast<uint4*>(scr + rr * S::kScratchRowBytes + pc * 16) = addv[i];
-          }
-          __syncwarp();
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const uint4 val = *reinterpret_cast<const uint4*>(scr + lane * S::kScratchRowBytes + i * 16);
-            const uint32_t w[4] = {val.x, val.y, val.z, val.w};
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              f[i * 8 + 2 * j] += __uint_as_float(w[j] << 16);
-              f[i * 8 + 2 * j + 1] += __uint_as_float(w[j] & 0xffff0000u);
-            }
-          }
-          __syncwarp();
-        }
-        if (p.flags & EPI_ARGMAX) {
-          if (row_ok) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const int n = n0 + c0 + j;
-              if (n < p.N) best = u64_max(best, pack_val_idx(f[j], (unsigned)n));
-            }
-          }
-        }
-        if (p.flags & EPI_OUT_F32) {
-          // f32 output: 32 cols = 128 bytes per row
-#pragma unroll
-          for (int i = 0; i < 8; ++i)
-            *reinterpret_cast<float4*>(scr + lane * S::kScratchRowBytes + i * 16) =
-                make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
-          __syncwarp();
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int piece = i * 32 + lane;  // 256 pieces of 4 f32: 8 per row
-            const int rr = piece >> 3, pc = piece & 7;
-            const int rb = row0 + lane_q * 32 + rr;
-            const int col = n0 + c0 + pc * 4;
-            if (rb < p.rows_per_batch && col < p.N) {
-              const float4 val = *reinterpret_cast<const float4*>(scr + rr * S::kScratchRowBytes + pc * 16);
-              float* dst = reinterpret_cast<float*>(p.C) + c_base + (long long)(rb - row0) * p.cmap.row_stride + col;
-              if (col + 3 < p.N && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-                *reinterpret_cast<float4*>(dst) = val;
-              } else {
-                const float tmp[4] = {val.x, val.y, val.z, val.w};
-                for (int q = 0; q < 4; ++q)
-                  if (col + q < p.N) dst[q] = tmp[q];
-              }
-            }
-          }
-          __syncwarp();
-        } else if (p.C != nullptr || (p.flags & EPI_SPLIT_KV)) {
-          // bf16 output: 32 cols = 64 bytes per row
-#pragma unroll
-          for (int i = 0; i < 4; ++i)
-            *reinterpret_cast<uint4*>(scr + lane * S::kScratchRowBytes + i * 16) =
-                make_uint4(pack_bf16x2(f[8 * i], f[8 * i + 1]), pack_bf16x2(f[8 * i + 2], f[8 * i + 3]),
-                           pack_bf16x2(f[8 * i + 4], f[8 * i + 5]), pack_bf16x2(f[8 * i + 6], f[8 * i + 7]));
-          __syncwarp();
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int piece = i * 32 + lane;
-            const int rr = piece >> 2, pc = piece & 3;
-            const int rb = row0 + lane_q * 32 + rr;
-            const int col = n0 + c0 + pc * 8;
-            if (rb < p.rows_per_batch && col < p.N) {
-              const uint4 val = *reinterpret_cast<const uint4*>(scr + rr * S::kScratchRowBytes + pc * 16);
-              if (p.flags & EPI_SPLIT_KV) {
-                int clip = batch, sq = rb;     // launched per clip (rows_per_batch == kv_S): no division
-                if (p.rows_per_batch != p.kv_S) {
-                  const int mm = batch * p.rows_per_batch + rb;
-                  clip = mm / p.kv_S;
-                  sq = mm - clip * p.kv_S;
-                }
-                const int dm = p.kv_H * 64;
-                const int which = col >= dm, cc = which ? col - dm : col;
-                __nv_bfloat16* dst;
-                if (p.kv_chunk > 0) {
-                  int ch = sq >> 7, kin = sq & 127;
-                  if (p.kv_chunk != 128) {
-                    ch = sq / p.kv_chunk;
-                    kin = sq - ch * p.kv_chunk;
-                  }
-                  // 16-byte segments of a key's 128-byte row are XOR-swizzled by key & 7: the decoder reads the chunk
-                  // with ldmatrix straight out of the bulk-copied stage (decoder_stream_sm100.cuh: ds_cross_attn)
-                  dst = p.kv_k + ((((size_t)(clip * p.kv_H + (cc >> 6)) * p.kv_cpp + ch) * 2 + which) * p.kv_chunk + kin) * 64 +
-                        (((((cc & 63) >> 3) ^ (kin & 7)) << 3));
-                } else {
-                  dst = (which ? p.kv_v : p.kv_k) + (((size_t)(clip * p.kv_H + (cc >> 6)) * p.kv_S + sq) * 64 + (cc & 63));
-                }
-                *reinterpret_cast<uint4*>(dst) = val;
-              } else {
-                *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C) + c_base +
-                                          (long long)(rb - row0) * p.cmap.row_stride + col) = val;
-              }
-            }
-          }
-          __syncwarp();
-        }
-      }
+      const unsigned long long best = gemm_epilogue_tile<BN, S::kScratchRowBytes>(p, t_row, bias_s, scr, lane, lane_q, batch, row0, n0);
       // accumulator fully read: hand it back to the MMA warp
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + acc);
-      if ((p.flags & EPI_ARGMAX) && row_ok) p.argmax_part[(long long)m * p.n_tiles_n + tn] = best;
+      if (p.flags & EPI_ARGMAX) {
+        const int r_batch = row0 + lane_q * 32 + lane;
+        if (r_batch < p.rows_per_batch) p.argmax_part[(long long)(batch * p.rows_per_batch + r_batch) * p.n_tiles_n + tn] = best;
+      }
     }
   }
 
@@ -538,6 +552,293 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, S::kTmemCols);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// CTA-pair variant (tcgen05 cta_group::2): a cluster of two CTAs computes a 256 x BN tile. Each CTA loads ITS 128 rows
+// of A and ITS half of the W tile (BN/2 rows); one tcgen05.mma.cta_group::2 (M = 256) issued by the leader drives both
+// SMs' tensor cores, each reading its own A and only half of W from its own shared memory — the operand traffic per
+// SM drops from 12 KB to 8 KB per MMA and the TMA writes from 48 KB to 32 KB per k-block, which is what the one-CTA
+// kernel above is bound by at K = 384 (192 B/clk of operand traffic against a 128 B/clk shared-memory port). The
+// accumulator of a CTA's 128 rows lives in its own tensor memory (2 stages), so the epilogue is unchanged.
+// Plumbing that differs: TMA loads of both CTAs complete on the LEADER's full barrier (.cta_group::2, the barrier's
+// address mapped into CTA 0); tcgen05.commit multicasts to both CTAs' empty / accumulator-full barriers; the peer's
+// epilogue warps release an accumulator stage on the leader's barrier (remote arrive); the leader's producer draws the
+// tile from the global counter and hands it to the peer's producer through a 4-entry inbox in the peer's shared memory.
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(cta));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {   // acquire at cluster scope: data a peer wrote
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P1;\n\t"
+      "WT_WAITC_LOOP:\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P1, [%0], %1;\n\t"
+      "@P1 bra WT_WAITC_DONE;\n\t"
+      "bra WT_WAITC_LOOP;\n\t"
+      "WT_WAITC_DONE:\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma2_load_2d(void* smem_dst, const CUtensorMap* map, uint32_t leader_bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(leader_bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma2_load_3d(void* smem_dst, const CUtensorMap* map, uint32_t leader_bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::
+          "r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(leader_bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void umma2_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on the barrier at this offset in BOTH CTAs of the pair once all previously issued tcgen05.mma have completed
+__device__ __forceinline__ void umma2_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(bar)),
+               "h"((uint16_t)3)
+               : "memory");
+}
+
+template <int BN>
+struct Gemm2Smem {
+  static constexpr int kABytes = kGemmBM * kGemmBK * 2;      // this CTA's 128 rows of A: 16 KB
+  static constexpr int kBBytes = (BN / 2) * kGemmBK * 2;     // this CTA's half of the W tile
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kScratchRowBytes = 128 + 16;
+  static constexpr int kScratchBytes = kGemmEpiGroups * 4 * 32 * kScratchRowBytes;
+  static constexpr int kBiasBytes = 4 * BN * 4;
+  static constexpr int kTileQ = 4;
+  static constexpr int kBarBytes = 512;
+  static constexpr int kFit = (232448 - 1024 - kScratchBytes - kBiasBytes - kBarBytes) / kStageBytes;
+  static constexpr int kStages = kFit > 8 ? 8 : kFit;
+  static constexpr int kTotal = kStages * kStageBytes + kScratchBytes + kBiasBytes + kBarBytes + 1024;
+  static constexpr int kTmemCols = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
+};
+
+// p.tiles_per_batch = ceil(rows_per_batch / 256) here; map_w has a box of BN/2 rows. grid = 2 x pairs, cluster (2,1,1).
+template <int BN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm2_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
+                        GemmBf16Params p) {
+  using S = Gemm2Smem<BN>;
+  extern __shared__ __align__(1024) uint8_t smem_dyn[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
+  uint8_t* s_stage = smem;
+  uint8_t* s_scratch = s_stage + S::kStages * S::kStageBytes;
+  float* s_bias = reinterpret_cast<float*>(s_scratch + S::kScratchBytes);
+  uint64_t* bar_full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(s_bias) + S::kBiasBytes);   // [8] (used in the leader)
+  uint64_t* bar_empty = bar_full + 8;              // [8] both CTAs (multicast commit)
+  uint64_t* bar_tfull = bar_empty + 8;             // [2] both CTAs (multicast commit)
+  uint64_t* bar_tempty = bar_tfull + 2;            // [2] leader: 4 local + 4 remote epilogue warps
+  uint64_t* bar_qfull = bar_tempty + 2;            // [kTileQ] local tile queue
+  uint64_t* bar_qempty = bar_qfull + S::kTileQ;    // [kTileQ]
+  uint64_t* bar_ifull = bar_qempty + S::kTileQ;    // [kTileQ] peer: inbox entry written by the leader's producer
+  uint64_t* bar_iempty = bar_ifull + S::kTileQ;    // [kTileQ] leader: inbox entry read by the peer's producer
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_iempty + S::kTileQ);
+  volatile int* s_tileq = reinterpret_cast<volatile int*>(s_tmem + 4);
+  volatile int* s_inbox = s_tileq + S::kTileQ;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int n_tiles_m = p.tiles_per_batch * p.n_batches;   // 256-row tiles
+  const int n_tiles = n_tiles_m * p.n_tiles_n;
+  const int n_kblocks = p.taps * p.kblocks_per_tap;
+  const int n_pairs = (int)gridDim.x >> 1, pair = (int)blockIdx.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_w);
+    for (int i = 0; i < 8; ++i) {
+      mbar_init(bar_full + i, 1);
+      mbar_init(bar_empty + i, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar_tfull + i, 1);
+      mbar_init(bar_tempty + i, 8);
+    }
+    for (int i = 0; i < S::kTileQ; ++i) {
+      mbar_init(bar_qfull + i, 1);
+      mbar_init(bar_qempty + i, leader ? 5 : 4);   // (MMA issuer +) 4 epilogue warps
+      mbar_init(bar_ifull + i, 1);
+      mbar_init(bar_iempty + i, 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"((uint32_t)S::kTmemCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();   // both CTAs' barriers exist before any remote arrive / multicast commit / cross-CTA TMA signal
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    // ================= TMA producer (both CTAs; the leader also schedules) =================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int n_end = 0;
+      int next_tile = pair;
+      const uint32_t peer_inbox = mapa_u32(smem_u32(const_cast<int*>(s_inbox)), 1);
+      for (int it = 0;; ++it) {
+        int tile;
+        const int is = it % S::kTileQ;
+        const uint32_t ipar = (uint32_t)(it / S::kTileQ) & 1u;
+        if (leader) {
+          tile = (n_end == 0) ? next_tile : n_tiles;
+          if (tile >= n_tiles) tile = -1;
+          if (tile >= 0) next_tile = n_pairs + atomicAdd(p.sched, 1);
+          // hand the tile to the peer's producer (inbox slot free once the peer has read entry it - kTileQ)
+          mbar_wait_cluster(bar_iempty + is, ipar ^ 1u);
+          asm volatile("st.shared::cluster.b32 [%0], %1;" ::"r"(peer_inbox + is * 4), "r"(tile) : "memory");
+          mbar_arrive_remote(mapa_u32(smem_u32(bar_ifull + is), 1));
+        } else {
+          mbar_wait_cluster(bar_ifull + is, ipar);
+          tile = s_inbox[is];
+          mbar_arrive_remote(mapa_u32(smem_u32(bar_iempty + is), 0));
+        }
+        const int qs = it % S::kTileQ;
+        mbar_wait(bar_qempty + qs, ((uint32_t)(it / S::kTileQ) & 1u) ^ 1u);
+        s_tileq[qs] = tile;
+        mbar_arrive(bar_qfull + qs);
+        if (tile < 0) {
+          if (++n_end == 2) break;     // one end marker per epilogue group
+          continue;
+        }
+        const int tn = tile % p.n_tiles_n, tm = tile / p.n_tiles_n;
+        const int batch = tm / p.tiles_per_batch, row0 = (tm % p.tiles_per_batch) * (2 * kGemmBM) + (int)rank * kGemmBM;
+        for (int kb = 0; kb < n_kblocks; ++kb) {
+          mbar_wait(bar_empty + stage, phase ^ 1);
+          uint8_t* sa = s_stage + stage * S::kStageBytes;
+          uint8_t* sb = sa + S::kABytes;
+          const uint32_t lbar = mapa_u32(smem_u32(bar_full + stage), 0);
+          if (leader) mbar_expect_tx(bar_full + stage, 2 * S::kStageBytes);   // both CTAs' bytes land on this barrier
+          const int tap = kb / p.kblocks_per_tap, kc = kb - tap * p.kblocks_per_tap;
+          tma2_load_3d(sa, &map_a, lbar, p.tap_c0[tap] + kc * kGemmBK, row0 + p.tap_row[tap], batch);
+          tma2_load_2d(sb, &map_w, lbar, tap * p.tap_k + kc * kGemmBK, tn * BN + (int)rank * (BN / 2));
+          if (++stage == S::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+      if (leader) {   // last pair out re-arms the scheduler for the next launch on this stream
+        __threadfence();
+        if (atomicAdd(p.sched + 1, 1) == n_pairs - 1) {
+          p.sched[0] = 0;
+          p.sched[1] = 0;
+          __threadfence();
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer (leader only) =================
+    if (leader) {
+      constexpr uint32_t idesc = make_idesc_bf16(2 * kGemmBM, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int it = 0;; ++it) {
+        const int qs = it % S::kTileQ;
+        mbar_wait(bar_qfull + qs, (uint32_t)(it / S::kTileQ) & 1u);
+        const int tile = s_tileq[qs];
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_qempty + qs);
+        if (tile < 0) break;
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait_cluster(bar_tempty + acc, acc_phase ^ 1);  // both CTAs' epilogues have drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < n_kblocks; ++kb) {
+          mbar_wait(bar_full + stage, phase);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t sa = smem_u32(s_stage + stage * S::kStageBytes);
+            const uint64_t da = make_sw128_desc(sa);
+            const uint64_t db = make_sw128_desc(sa + S::kABytes);
+#pragma unroll
+            for (int k = 0; k < kGemmBK / 16; ++k) umma2_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma2_commit(bar_empty + stage);                       // both CTAs' slots reusable once these MMAs retire
+            if (kb == n_kblocks - 1) umma2_commit(bar_tfull + acc);  // both CTAs' accumulator halves complete
+          }
+          __syncwarp();
+          if (++stage == S::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else {
+    // ================= epilogue (both CTAs: their own 128 rows) =================
+    const int ew = warp - 2;
+    const int eg = ew >> 2;
+    const int lane_q = warp & 3;
+    const int et = (threadIdx.x - 64) & 127;
+    uint8_t* scr = s_scratch + ew * 32 * S::kScratchRowBytes;
+    for (int it = eg;; it += 2) {
+      const int acc = eg;
+      const int qs = it % S::kTileQ;
+      mbar_wait(bar_qfull + qs, (uint32_t)(it / S::kTileQ) & 1u);
+      const int tile = s_tileq[qs];
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_qempty + qs);
+      if (tile < 0) break;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      const int tn = tile % p.n_tiles_n, tm = tile / p.n_tiles_n;
+      const int batch = tm / p.tiles_per_batch, row0 = (tm % p.tiles_per_batch) * (2 * kGemmBM) + (int)rank * kGemmBM;
+      const int n0 = tn * BN;
+      float* bias_s = s_bias + (acc * 2 + ((it >> 1) & 1)) * BN;
+      if (p.flags & EPI_BIAS)
+        for (int i = et; i < BN; i += 128) bias_s[i] = (n0 + i < p.N) ? __ldg(p.bias + n0 + i) : 0.0f;
+      asm volatile("bar.sync %0, 128;" ::"r"(1 + eg) : "memory");
+      mbar_wait(bar_tfull + acc, acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(lane_q * 32) << 16) + acc * BN;
+      const unsigned long long best = gemm_epilogue_tile<BN, S::kScratchRowBytes>(p, t_row, bias_s, scr, lane, lane_q, batch, row0, n0);
+      // accumulator fully read: hand it back to the leader's MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_remote(mapa_u32(smem_u32(bar_tempty + acc), 0));
+      if (p.flags & EPI_ARGMAX) {
+        const int r_batch = row0 + lane_q * 32 + lane;
+        if (r_batch < p.rows_per_batch) p.argmax_part[(long long)(batch * p.rows_per_batch + r_batch) * p.n_tiles_n + tn] = best;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();   // no CTA leaves (or frees tensor memory) while its peer may still signal it
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)S::kTmemCols) : "memory");
   }
 }
 
