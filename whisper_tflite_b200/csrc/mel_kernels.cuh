@@ -183,17 +183,21 @@ __device__ __forceinline__ int bitrev4(int i) { return ((i & 1) << 3) | ((i & 2)
 
 __device__ __forceinline__ int pcm_phys(int i) { return i + 16 * (i / kHop); }
 
+// Shared memory: PCM span | exchange (one slot per frame in flight; the frame's power spectrum is written back over its
+// own slot once the FFT-16 has read it) | output stage | Hann window | W_400 twiddles [k][r] | reduction scratch.
+// 71 KB: three blocks per SM (the tables live here instead of 51 registers per thread: 112 -> <= 80 registers).
 constexpr int kMelSmemBytes =
-    (kSpanPhys + 2 * 16 * kExStride + 16 * kPsStride + kMaxMel * kOutStride + 8) * (int)sizeof(float);
+    (kSpanPhys + 2 * 16 * kExStride + kMaxMel * kOutStride + kFFT + 2 * 16 * 13 + 8) * (int)sizeof(float);
 
 // grid = (n_tiles, B); block = 256
-__global__ void __launch_bounds__(kMelThreads, 2) mel_frames_kernel(MelParams p) {
+__global__ void __launch_bounds__(kMelThreads, 3) mel_frames_kernel(MelParams p) {
   WT_DYN_SMEM(smem_raw);
   float* s_pcm = reinterpret_cast<float*>(smem_raw);
   float2* s_ex = reinterpret_cast<float2*>(s_pcm + kSpanPhys);
-  float* s_ps = reinterpret_cast<float*>(s_ex + 16 * kExStride);
-  float* s_out = s_ps + 16 * kPsStride;
-  float* s_red = s_out + kMaxMel * kOutStride;  // 8 floats
+  float* s_out = reinterpret_cast<float*>(s_ex + 16 * kExStride);
+  float* s_hann = s_out + kMaxMel * kOutStride;                   // [400]
+  float2* s_tw = reinterpret_cast<float2*>(s_hann + kFFT);        // [13][16]: (cos, -sin)(2 pi r k / 400) at [k][r]
+  float* s_red = reinterpret_cast<float*>(s_tw + 16 * 13);        // 8 floats
 
   const int tid = threadIdx.x;
   const int tile = blockIdx.x;
@@ -247,13 +251,9 @@ __global__ void __launch_bounds__(kMelThreads, 2) mel_frames_kernel(MelParams p)
   }
   }
 
-  // ---- per-lane constants: Hann for this residue, W_400^{r k'} ----
-  float hann[25];
-  float2 tw[13];
-#pragma unroll
-  for (int m = 0; m < 25; ++m) hann[m] = __ldg(p.hann + 16 * m + lane16);
-#pragma unroll
-  for (int k = 0; k < 13; ++k) tw[k] = __ldg(p.tw400 + lane16 * 13 + k);
+  // ---- tables: Hann window, W_400^{r k'} transposed to [k'][r] (lanes of a half-warp read consecutive words) ----
+  for (int i = tid; i < kFFT; i += kMelThreads) s_hann[i] = __ldg(p.hann + i);
+  if (tid < 16 * 13) s_tw[(tid % 13) * 16 + tid / 13] = __ldg(p.tw400 + tid);
   __syncthreads();
 
   float vmax = -3.0e38f;
@@ -264,21 +264,22 @@ __global__ void __launch_bounds__(kMelThreads, 2) mel_frames_kernel(MelParams p)
     {
       float a[25];
 #pragma unroll
-      for (int m = 0; m < 25; ++m) a[m] = hann[m] * s_pcm[pcm_phys(fl * kHop + 16 * m + lane16)];
+      for (int m = 0; m < 25; ++m) a[m] = s_hann[16 * m + lane16] * s_pcm[pcm_phys(fl * kHop + 16 * m + lane16)];
       cpx S[13];
       rdft25(a, S);
       float2* ex = s_ex + fslot * kExStride + lane16 * 13;
       ex[0] = make_float2(S[0].re, S[0].im);
 #pragma unroll
       for (int k = 1; k < 13; ++k) {
-        cpx t = cmul(S[k], tw[k].x, tw[k].y);
+        const float2 w = s_tw[k * 16 + lane16];
+        cpx t = cmul(S[k], w.x, w.y);
         ex[k] = make_float2(t.re, t.im);
       }
     }
     __syncwarp();
     // ---- C: complex FFT-16 over r for k' = lane16 < 13, power, scatter to bins ----
+    cpx v[16];
     if (lane16 < 13) {
-      cpx v[16];
       const float2* ex = s_ex + fslot * kExStride + lane16;
 #pragma unroll
       for (int r = 0; r < 16; ++r) {
@@ -286,7 +287,11 @@ __global__ void __launch_bounds__(kMelThreads, 2) mel_frames_kernel(MelParams p)
         v[r] = {t.x, t.y};
       }
       fft16_dif(v);
-      float* ps = s_ps + fslot * kPsStride;
+    }
+    // the power spectrum goes over the frame's own exchange slot: every lane of the half-warp has read its 16 values
+    __syncwarp();
+    if (lane16 < 13) {
+      float* ps = reinterpret_cast<float*>(s_ex + fslot * kExStride);
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
         const int q = bitrev4(i);
@@ -303,7 +308,7 @@ __global__ void __launch_bounds__(kMelThreads, 2) mel_frames_kernel(MelParams p)
     __syncwarp();
     // ---- D: mel rows lane16, lane16+16, ... ; log10(max(.,1e-10)) (whisper.cpp:169-184) ----
     {
-      const float* ps = s_ps + fslot * kPsStride;
+      const float* ps = reinterpret_cast<const float*>(s_ex + fslot * kExStride);
       for (int j = lane16; j < p.n_mel; j += 16) {
         const int2 row = __ldg(p.frow + j);
         const int len = __ldg(p.flen + j);
