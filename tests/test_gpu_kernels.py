@@ -89,6 +89,33 @@ def test_gemm_residual_add_in_place(M, N, K):
     assert (x.float() - ref).abs().max().item() <= _tol(ref)
 
 
+@pytest.mark.parametrize("add", [0, 1])
+@pytest.mark.parametrize("T,N,K", [(300, 384, 384), (1500, 384, 1536), (92, 1152, 384)])
+def test_gemm_tma_store_clips_at_clip_end(T, N, K, add):
+    """Per-clip batches into a padded C [B][T + 8][N] (and, with add, a residual read from a differently padded buffer):
+    the epilogue's bulk tensor stores must clip at row T of every clip — the guard rows keep their sentinel — and the
+    ragged last 128-row tile of a clip must not leak into the next clip."""
+    import torch
+    from whisper_tflite_b200 import capi
+    B = 3
+    g = torch.Generator(device="cuda").manual_seed(T + N + add)
+    a = (torch.randn(B, T, K, device="cuda", generator=g) * 0.5).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) * 0.1).bfloat16()
+    b = torch.randn(N, device="cuda", generator=g)
+    out = torch.full((B, T + 8, N), 7.0, device="cuda", dtype=torch.bfloat16)
+    res = torch.randn(B, T + 16, N, device="cuda", generator=g).bfloat16()
+    ref = a.float() @ w.float().T + b
+    kw = dict(A=a, a_dims=[K, T, B], a_strides=[K * 2, T * K * 2], rows_per_batch=T, n_batches=B, W=w, bias=b, N=N,
+              K_total=K, taps=1, C=out, c_batch_stride=(T + 8) * N, c_rows=T, c_row_stride=N, flags=capi.EPI_BIAS)
+    if add:
+        ref = ref + res[:, :T].float()
+        kw.update(addend=res, add_batch_stride=(T + 16) * N, add_rows=T, add_row_stride=N, flags=capi.EPI_BIAS | capi.EPI_ADD)
+    capi.debug_gemm_ex(**kw)
+    torch.cuda.synchronize()
+    assert (out[:, T:].float() == 7.0).all()
+    assert (out[:, :T].float() - ref).abs().max().item() <= _tol(ref)
+
+
 @pytest.mark.parametrize("stride,cin,T", [(1, 80, 3000), (2, 384, 3000), (1, 80, 200), (2, 128, 256)])
 def test_gemm_three_tap_conv_vs_torch_conv1d(stride, cin, T):
     """conv1 (stride 1, 80 -> d) and conv2 (stride 2, d -> d) as 3-tap GEMMs over the zero-padded time-major activation

@@ -167,9 +167,11 @@ EncodeTiledFn get_encode_tiled() {
   return fn;
 }
 
-// bf16 tensor, 128B swizzle, inner box 64 elements. dims/strides innermost first; strides in bytes for dims 1..rank-1.
+// bf16 tensor; inner box 64 elements with the 128B swizzle, or 32 elements with the 64B swizzle. dims/strides innermost
+// first; strides in bytes for dims 1..rank-1.
 int make_map_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                   const uint32_t* box) {
+  const CUtensorMapSwizzle swz = box[0] == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
   EncodeTiledFn fn = get_encode_tiled();
   if (!fn) return fail(WT_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
   cuuint64_t gd[5];
@@ -182,7 +184,7 @@ int make_map_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* 
     if (i > 0) gs[i - 1] = strides_bytes[i - 1];
   }
   CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
     return fail(WT_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) rank=%d dims=[%llu,%llu,%llu] stride0=%llu", (int)r,
@@ -377,7 +379,7 @@ struct wt_engine {
 int wt_engine::get_map(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides,
                        const uint32_t* box) {
   auto key = std::make_tuple(base, dims[0], rank > 1 ? dims[1] : 0, rank > 2 ? dims[2] : 0, rank > 1 ? strides[0] : 0,
-                             rank > 2 ? strides[1] : 0, (uint32_t)(box[1] * 4 + rank));
+                             rank > 2 ? strides[1] : 0, (uint32_t)((box[0] << 16) + box[1] * 4 + rank));
   auto it = map_cache.find(key);
   if (it != map_cache.end()) {
     *out = it->second;
@@ -389,7 +391,7 @@ int wt_engine::get_map(CUtensorMap* out, const void* base, int rank, const uint6
 }
 
 template <int BN>
-static int launch_gemm_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMap& mw, wt::GemmBf16Params& p) {
+static int launch_gemm_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mc, const CUtensorMap& mr, wt::GemmBf16Params& p) {
   using S = wt::GemmSmem<BN>;
   p.n_tiles_n = (p.N + BN - 1) / BN;
   const int n_tiles = p.tiles_per_batch * p.n_batches * p.n_tiles_n;
@@ -397,13 +399,13 @@ static int launch_gemm_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMap
   if (!e->gemm_sched) return fail(WT_ERR_STATE, "GEMM tile scheduler not allocated (engine not initialised)");
   p.sched = e->gemm_sched;
   e->pre_launch();
-  wt::gemm_bf16_sm100_kernel<BN><<<grid, wt::kGemmThreads, S::kTotal, e->stream>>>(ma, mw, p);
+  wt::gemm_bf16_sm100_kernel<BN><<<grid, wt::kGemmThreads, S::kTotal, e->stream>>>(ma, mw, mc, mr, p);
   return e->check_launch("gemm_bf16_sm100_kernel");
 }
 
 // CTA-pair kernel (gemm2_bf16_sm100_kernel): 256-row tiles on a cluster of two CTAs
 template <int BN>
-static int launch_gemm2_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMap& mw, wt::GemmBf16Params& p) {
+static int launch_gemm2_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mc, const CUtensorMap& mr, wt::GemmBf16Params& p) {
   using S = wt::Gemm2Smem<BN>;
   p.n_tiles_n = (p.N + BN - 1) / BN;
   const int n_tiles = p.tiles_per_batch * p.n_batches * p.n_tiles_n;
@@ -412,7 +414,7 @@ static int launch_gemm2_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMa
   if (!e->gemm_sched) return fail(WT_ERR_STATE, "GEMM tile scheduler not allocated (engine not initialised)");
   p.sched = e->gemm_sched;
   e->pre_launch();
-  wt::gemm2_bf16_sm100_kernel<BN><<<2 * pairs, wt::kGemmThreads, S::kTotal, e->stream>>>(ma, mw, p);
+  wt::gemm2_bf16_sm100_kernel<BN><<<2 * pairs, wt::kGemmThreads, S::kTotal, e->stream>>>(ma, mw, mc, mr, p);
   return e->check_launch("gemm2_bf16_sm100_kernel");
 }
 // Where the pair wins (tools/gemm_bench.py, M = 96 000): K >= 768 — fc2 at K = 1536 / 2048 / 3072: 119 -> 111, 193 -> 152,
@@ -478,19 +480,49 @@ int wt_engine::gemm_bf16(const void* A, const uint64_t* a_dims, const uint64_t* 
     p.tap_c0[i] = (i < taps && tap_c0) ? tap_c0[i] : 0;
     p.tap_row[i] = (i < taps && tap_row) ? tap_row[i] : 0;
   }
+  // C through TMA (EPI_TMA_C): a bf16 C whose RowMap is a 3-D tensor {N, rows_per_batch, batches} with 16-byte aligned
+  // base and strides. Rows past a clip's end and columns past N are clipped by the map's extents. With an addend that
+  // has such a map as well (EPI_TMA_ADD: the residual GEMMs) both directions go through 32 x 32 boxes, the addend
+  // prefetched by the copy engine a chunk ahead and updated in place in shared memory.
+  CUtensorMap mc = ma, mr = ma;
+  {
+    static const char* ov = getenv("WT_GEMM_TMA_C");   // "0": the epilogue warps load / store themselves; "1": no TMA addend
+    auto as_tensor = [&](const void* base, const RowMap& m, long long& bstride) {
+      bstride = -1;
+      if (m.rows_per_batch == rows_per_batch) bstride = n_batches > 1 ? m.batch_stride : (long long)rows_per_batch * m.row_stride;
+      else if (m.rows_per_batch >= M) bstride = (long long)rows_per_batch * m.row_stride;
+      return base != nullptr && (reinterpret_cast<uintptr_t>(base) & 15) == 0 && m.row_stride > 0 && (m.row_stride * 2) % 16 == 0 &&
+             bstride > 0 && (bstride * 2) % 16 == 0;
+    };
+    const bool plain_out = !(flags & (wt::EPI_OUT_F32 | wt::EPI_ARGMAX | wt::EPI_SPLIT_KV));
+    long long cb = 0, rb = 0;
+    if (plain_out && as_tensor(C, cmap, cb) && L.N >= 64 && bn >= 64 && !(ov && ov[0] == '0')) {
+      const bool tma_add = (flags & wt::EPI_ADD) && as_tensor(addend, add_map, rb) && !(ov && ov[0] == '1');
+      const uint64_t cdims[3] = {(uint64_t)L.N, (uint64_t)rows_per_batch, (uint64_t)n_batches};
+      const uint64_t cstr[2] = {(uint64_t)cmap.row_stride * 2, (uint64_t)cb * 2};
+      const uint32_t cbox[3] = {tma_add ? 32u : 64u, 32, 1};
+      WT_TRY(get_map(&mc, C, 3, cdims, cstr, cbox));
+      p.flags |= wt::EPI_TMA_C;
+      if (tma_add) {
+        const uint64_t rstr[2] = {(uint64_t)add_map.row_stride * 2, (uint64_t)rb * 2};
+        WT_TRY(get_map(&mr, addend, 3, cdims, rstr, cbox));
+        p.flags |= wt::EPI_TMA_ADD;
+      }
+    }
+  }
   if (pair) {
     p.tiles_per_batch = (rows_per_batch + 255) / 256;
     switch (bn) {
-      case 128: return launch_gemm2_bn<128>(this, ma, mw, p);
-      case 192: return launch_gemm2_bn<192>(this, ma, mw, p);
-      case 256: return launch_gemm2_bn<256>(this, ma, mw, p);
+      case 128: return launch_gemm2_bn<128>(this, ma, mw, mc, mr, p);
+      case 192: return launch_gemm2_bn<192>(this, ma, mw, mc, mr, p);
+      case 256: return launch_gemm2_bn<256>(this, ma, mw, mc, mr, p);
     }
   }
   switch (bn) {
-    case 64: return launch_gemm_bn<64>(this, ma, mw, p);
-    case 128: return launch_gemm_bn<128>(this, ma, mw, p);
-    case 192: return launch_gemm_bn<192>(this, ma, mw, p);
-    case 256: return launch_gemm_bn<256>(this, ma, mw, p);
+    case 64: return launch_gemm_bn<64>(this, ma, mw, mc, mr, p);
+    case 128: return launch_gemm_bn<128>(this, ma, mw, mc, mr, p);
+    case 192: return launch_gemm_bn<192>(this, ma, mw, mc, mr, p);
+    case 256: return launch_gemm_bn<256>(this, ma, mw, mc, mr, p);
   }
   return fail(WT_ERR_INVALID, "bad BN %d", bn);
 }

@@ -37,6 +37,10 @@ constexpr int kGemmEpiGroups = 2;   // epilogue warp groups (4 warps each): grou
 constexpr int kGemmThreads = 64 + kGemmEpiGroups * 128;
 
 enum : int { EPI_ADD = 4, EPI_OUT_F32 = 16, EPI_ARGMAX = 32, EPI_SPLIT_KV = 64 };  // EPI_BIAS = 1, EPI_GELU = 2 shared with SIMT
+// set by the host when C (bf16) is expressible as a 3-D tensor map {N, rows_per_batch, batches}: the epilogue warps hand
+// their 32 x 64 pieces of the tile to TMA (cp.async.bulk.tensor store) instead of issuing the global stores themselves
+constexpr int EPI_TMA_C = 128;
+constexpr int EPI_TMA_ADD = 256;   // with EPI_TMA_C and EPI_ADD: the addend has a tensor map too (see gemm_epilogue_tile)
 
 struct GemmBf16Params {
   const float* bias;               // [N] f32 or null
@@ -130,6 +134,16 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m
       "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
+// store of a {64 bf16, 32 rows, 1} box from shared memory; rows / columns outside the tensor map's extents are clipped
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
 }
@@ -205,21 +219,30 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&t);
 }
 
+// Per-warp epilogue scratch on a 1024-byte boundary, used in one of two layouts. TMA store (EPI_TMA_C): 32 rows x 128
+// bytes, 16-byte pieces XOR-swizzled by (row & 7) — what CU_TENSOR_MAP_SWIZZLE_128B expects of a {64 bf16, 32 rows} box,
+// conflict-free for one-row-per-lane access. Otherwise: rows of 128 + 16 bytes (64 bf16 or 32 f32 + pad), which keeps both
+// the row-per-lane and the coalesced four-pieces-per-row phases of a transpose conflict-free.
+constexpr int kGemmScrBytes = 6144;   // three 2 KB boxes (EPI_TMA_ADD) / one 4 KB box (EPI_TMA_C) / 32 padded rows
+constexpr int kGemmScrRow = 128 + 16;
+__device__ __forceinline__ uint8_t* scr_piece(uint8_t* scr, int row, int chunk) {
+  return scr + row * 128 + ((chunk ^ (row & 7)) << 4);
+}
+
 template <int BN>
 struct GemmSmem {
   static constexpr int kStages = (BN <= 64) ? 6 : (BN <= 128) ? 5 : (BN <= 192) ? 4 : 3;
   static constexpr int kABytes = kGemmBM * kGemmBK * 2;  // 16 KB
   static constexpr int kBBytes = BN * kGemmBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kScratchRowBytes = 128 + 16;  // 64 bf16 or 32 f32 per row + pad (keeps 16B phases conflict-free)
-  static constexpr int kScratchBytes = kGemmEpiGroups * 4 * 32 * kScratchRowBytes;
+  static constexpr int kScratchBytes = kGemmEpiGroups * 4 * kGemmScrBytes;
   // bias staging: per epilogue group TWO buffers, alternating with the group's tiles. A warp that has finished tile i
   // writes tile i+2's bias (other n0) while a slower warp of the group may still be reading tile i's: with one buffer
   // that was a write-after-read race (the run-to-run token differences of round 1); with two, the writer of tile i+4's
   // bias has passed tile i+2's group barrier, which every warp reaches only after its last read of tile i's buffer.
   static constexpr int kBiasBytes = 4 * BN * 4;
   static constexpr int kTileQ = 4;      // tile-index queue producer -> MMA issuer + epilogue group (even: it & 1 keeps its group)
-  static constexpr int kBarBytes = (2 * kStages + 4 + 2 * kTileQ) * 8 + 16 + kTileQ * 4;
+  static constexpr int kBarBytes = (2 * kStages + 4 + 2 * kTileQ + 24) * 8 + 16 + kTileQ * 4;
   static constexpr int kTotal = kStages * kStageBytes + kScratchBytes + kBiasBytes + kBarBytes + 1024;
   static constexpr int kTmemCols = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
 };
@@ -228,14 +251,92 @@ struct GemmSmem {
 // 32-column chunks -> + bias -> GELU -> + addend -> bf16 (or f32) -> transpose through the warp's scratch -> 16-byte
 // coalesced stores through the RowMap, or the K/V-stream scatter, or the fused (max, last index). Returns the row's
 // packed winner (EPI_ARGMAX). Shared by the one-CTA and the CTA-pair kernels.
-template <int BN, int kScrRow>
-__device__ __forceinline__ unsigned long long gemm_epilogue_tile(const GemmBf16Params& p, uint32_t t_row, const float* bias_s,
-                                                                  uint8_t* scr, int lane, int lane_q, int batch, int row0,
-                                                                  int n0) {
+// EPI_TMA_ADD: the first two addend boxes of a tile, requested as soon as the tile is known (before its accumulator is)
+__device__ __forceinline__ void gemm_epilogue_prefetch_add(const GemmBf16Params& p, const CUtensorMap* map_add, uint64_t* bar_add,
+                                                           uint8_t* scr, int lane, int lane_q, int batch, int row0, int n0) {
+  if ((p.flags & EPI_TMA_ADD) && lane == 0) {
+    bulk_wait_read0();   // the previous tile's last two stores have read their boxes
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      mbar_expect_tx(bar_add + b, 2048);
+      tma_load_3d(scr + b * 2048, map_add, bar_add + b, n0 + b * 32, row0 + lane_q * 32, batch);
+    }
+  }
+  __syncwarp();
+}
+
+template <int BN>
+__device__ __forceinline__ unsigned long long gemm_epilogue_tile(const GemmBf16Params& p, const CUtensorMap* map_c,
+                                                                  const CUtensorMap* map_add, uint64_t* bar_add, uint32_t& add_ph,
+                                                                  uint32_t t_row, const float* bias_s, uint8_t* scr, int lane,
+                                                                  int lane_q, int batch, int row0, int n0) {
   const int r_in_tile = lane_q * 32 + lane;           // accumulator row owned by this thread
   const int r_batch = row0 + r_in_tile;               // row within the clip
   const bool row_ok = r_batch < p.rows_per_batch;
+  const bool tma_c = (p.flags & EPI_TMA_C) != 0;
   unsigned long long best = 0ull;
+  if (p.flags & EPI_TMA_ADD) {
+    // Residual GEMMs: addend in and result out through 32 x 32 boxes (64-byte rows, 16-byte pieces XOR-swizzled by
+    // (row >> 1) & 3 = CU_TENSOR_MAP_SWIZZLE_64B), three boxes per warp in rotation. Chunks 0 and 1 were requested by
+    // gemm_epilogue_prefetch_add before the accumulator was waited for; chunk c + 2's addend is requested when chunk c's
+    // result has been handed to the copy engine (into the box chunk c - 1 went out of: its store has had a whole chunk
+    // to read it). A lane adds its row in place and the box goes back out with one bulk store.
+    constexpr int kChunks = BN / 32;
+    const int rowq = row0 + lane_q * 32;
+    int b = 0;   // c % 3
+#pragma unroll 1
+    for (int c = 0; c < kChunks; ++c) {
+      uint32_t v[32];
+      tmem_ld32(t_row + c * 32, v);
+      tmem_ld_wait();
+      float f[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+      if (p.flags & EPI_BIAS) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const float4 b4 = *reinterpret_cast<const float4*>(bias_s + c * 32 + j);
+          f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
+        }
+      }
+      if (p.flags & EPI_GELU) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = gelu_tanh_fit(f[j]);
+      }
+      mbar_wait(bar_add + b, (add_ph >> b) & 1u);
+      add_ph ^= 1u << b;
+      uint8_t* box = scr + b * 2048 + lane * 64;
+      const int sw = (lane >> 1) & 3;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint4* pc = reinterpret_cast<uint4*>(box + ((i ^ sw) << 4));
+        const uint4 val = *pc;
+        const uint32_t w[4] = {val.x, val.y, val.z, val.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          f[i * 8 + 2 * j] += __uint_as_float(w[j] << 16);
+          f[i * 8 + 2 * j + 1] += __uint_as_float(w[j] & 0xffff0000u);
+        }
+        *pc = make_uint4(pack_bf16x2(f[8 * i], f[8 * i + 1]), pack_bf16x2(f[8 * i + 2], f[8 * i + 3]),
+                         pack_bf16x2(f[8 * i + 4], f[8 * i + 5]), pack_bf16x2(f[8 * i + 6], f[8 * i + 7]));
+      }
+      fence_proxy_async();
+      __syncwarp();
+      const int bn = b == 2 ? 0 : b + 1, bp = b == 0 ? 2 : b - 1;
+      if (lane == 0) {
+        tma_store_3d(map_c, scr + b * 2048, n0 + c * 32, rowq, batch);
+        bulk_commit();
+        if (c + 2 < kChunks) {
+          asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // every store but chunk c's has read its box
+          mbar_expect_tx(bar_add + bp, 2048);
+          tma_load_3d(scr + bp * 2048, map_add, bar_add + bp, n0 + (c + 2) * 32, rowq, batch);
+        }
+      }
+      __syncwarp();
+      b = bn;
+    }
+    return 0ull;
+  }
   // a tile never straddles a batch: one RowMap division per tile, rows are then row_stride apart
   const long long c_base = p.cmap.at(batch * p.rows_per_batch + row0);
   const long long a_base = (p.flags & EPI_ADD) ? p.add_map.at(batch * p.rows_per_batch + row0) : 0ll;
@@ -273,6 +374,13 @@ __device__ __forceinline__ unsigned long long gemm_epilogue_tile(const GemmBf16P
 #pragma unroll
       for (int j = 0; j < 32; ++j) f[j] = gelu_tanh_fit(f[j]);
     }
+    // TMA store: columns c0 .. c0+31 are the left (half 0) or right half of a 64-column store box; the box of the
+    // previous pair must have been read out of the scratch before anything is written into it again
+    const int half4 = tma_c ? ((c0 >> 3) & 4) : 0;
+    if (tma_c && half4 == 0) {
+      if (lane == 0) bulk_wait_read0();
+      __syncwarp();
+    }
     if (p.flags & EPI_ADD) {
       // coalesced fetch of this warp's 32 rows x 32 cols of the addend through the scratch
       __syncwarp();
@@ -280,12 +388,12 @@ __device__ __forceinline__ unsigned long long gemm_epilogue_tile(const GemmBf16P
       for (int i = 0; i < 4; ++i) {
         const int piece = i * 32 + lane;
         const int rr = piece >> 2, pc = piece & 3;
-        *reinterpret_cast<uint4*>(scr + rr * kScrRow + pc * 16) = addv[i];
+        *reinterpret_cast<uint4*>(tma_c ? scr_piece(scr, rr, half4 + pc) : scr + rr * kGemmScrRow + pc * 16) = addv[i];
       }
       __syncwarp();
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        const uint4 val = *reinterpret_cast<const uint4*>(scr + lane * kScrRow + i * 16);
+        const uint4 val = *reinterpret_cast<const uint4*>(tma_c ? scr_piece(scr, lane, half4 + i) : scr + lane * kGemmScrRow + i * 16);
         const uint32_t w[4] = {val.x, val.y, val.z, val.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -308,8 +416,7 @@ __device__ __forceinline__ unsigned long long gemm_epilogue_tile(const GemmBf16P
       // f32 output: 32 cols = 128 bytes per row
 #pragma unroll
       for (int i = 0; i < 8; ++i)
-        *reinterpret_cast<float4*>(scr + lane * kScrRow + i * 16) =
-            make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+        *reinterpret_cast<float4*>(scr + lane * kGemmScrRow + i * 16) = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
       __syncwarp();
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -318,7 +425,7 @@ __device__ __forceinline__ unsigned long long gemm_epilogue_tile(const GemmBf16P
         const int rb = row0 + lane_q * 32 + rr;
         const int col = n0 + c0 + pc * 4;
         if (rb < p.rows_per_batch && col < p.N) {
-          const float4 val = *reinterpret_cast<const float4*>(scr + rr * kScrRow + pc * 16);
+          const float4 val = *reinterpret_cast<const float4*>(scr + rr * kGemmScrRow + pc * 16);
           float* dst = reinterpret_cast<float*>(p.C) + c_base + (long long)(rb - row0) * p.cmap.row_stride + col;
           if (col + 3 < p.N && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
             *reinterpret_cast<float4*>(dst) = val;
@@ -330,11 +437,27 @@ __device__ __forceinline__ unsigned long long gemm_epilogue_tile(const GemmBf16P
         }
       }
       __syncwarp();
+    } else if (tma_c) {
+      // bf16 output through TMA: this lane's 64 bytes into its row of the swizzled box; every second chunk one lane
+      // hands the 32 x 64 box to the copy engine (rows beyond the clip and columns beyond N are clipped by the map)
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<uint4*>(scr_piece(scr, lane, half4 + i)) =
+            make_uint4(pack_bf16x2(f[8 * i], f[8 * i + 1]), pack_bf16x2(f[8 * i + 2], f[8 * i + 3]),
+                       pack_bf16x2(f[8 * i + 4], f[8 * i + 5]), pack_bf16x2(f[8 * i + 6], f[8 * i + 7]));
+      if (half4 != 0) {
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_3d(map_c, scr, n0 + c0 - 32, row0 + lane_q * 32, batch);
+          bulk_commit();
+        }
+      }
     } else if (p.C != nullptr || (p.flags & EPI_SPLIT_KV)) {
       // bf16 output: 32 cols = 64 bytes per row
 #pragma unroll
       for (int i = 0; i < 4; ++i)
-        *reinterpret_cast<uint4*>(scr + lane * kScrRow + i * 16) =
+        *reinterpret_cast<uint4*>(scr + lane * kGemmScrRow + i * 16) =
             make_uint4(pack_bf16x2(f[8 * i], f[8 * i + 1]), pack_bf16x2(f[8 * i + 2], f[8 * i + 3]),
                        pack_bf16x2(f[8 * i + 4], f[8 * i + 5]), pack_bf16x2(f[8 * i + 6], f[8 * i + 7]));
       __syncwarp();
@@ -345,7 +468,7 @@ __device__ __forceinline__ unsigned long long gemm_epilogue_tile(const GemmBf16P
         const int rb = row0 + lane_q * 32 + rr;
         const int col = n0 + c0 + pc * 8;
         if (rb < p.rows_per_batch && col < p.N) {
-          const uint4 val = *reinterpret_cast<const uint4*>(scr + rr * kScrRow + pc * 16);
+          const uint4 val = *reinterpret_cast<const uint4*>(scr + rr * kGemmScrRow + pc * 16);
           if (p.flags & EPI_SPLIT_KV) {
             int clip = batch, sq = rb;     // launched per clip (rows_per_batch == kv_S): no division
             if (p.rows_per_batch != p.kv_S) {
@@ -385,7 +508,8 @@ __device__ __forceinline__ unsigned long long gemm_epilogue_tile(const GemmBf16P
 template <int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
-                       GemmBf16Params p) {
+                       const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_add,
+    GemmBf16Params p) {
   using S = GemmSmem<BN>;
   extern __shared__ __align__(1024) uint8_t smem_dyn[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
@@ -398,7 +522,8 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
   uint64_t* bar_tempty = bar_tfull + 2;           // [2]
   uint64_t* bar_qfull = bar_tempty + 2;           // [kTileQ] tile index published
   uint64_t* bar_qempty = bar_qfull + S::kTileQ;   // [kTileQ] read by the MMA issuer and the four warps of one epilogue group
-  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_qempty + S::kTileQ);
+  uint64_t* bar_addend = bar_qempty + S::kTileQ;  // [8 epilogue warps][3] addend boxes landed (EPI_TMA_ADD)
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_addend + 24);
   volatile int* s_tileq = reinterpret_cast<volatile int*>(s_tmem + 4);
 
   const int warp = threadIdx.x >> 5;
@@ -410,6 +535,8 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_w);
+    if (p.flags & EPI_TMA_C) tma_prefetch_desc(&map_c);
+    if (p.flags & EPI_TMA_ADD) tma_prefetch_desc(&map_add);
     for (int i = 0; i < S::kStages; ++i) {
       mbar_init(bar_full + i, 1);
       mbar_init(bar_empty + i, 1);
@@ -422,6 +549,7 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
       mbar_init(bar_qfull + i, 1);
       mbar_init(bar_qempty + i, 5);  // MMA issuer + 4 epilogue warps
     }
+    for (int i = 0; i < 24; ++i) mbar_init(bar_addend + i, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(s_tmem, S::kTmemCols);
@@ -515,7 +643,9 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
     const int eg = ew >> 2;             // epilogue group: drains tiles with (it & 1) == eg
     const int lane_q = warp & 3;        // TMEM lane quarter this warp may touch: lanes 32*(warp%4)..+31
     const int et = (threadIdx.x - 64) & 127;  // 0..127 within the group
-    uint8_t* scr = s_scratch + ew * 32 * S::kScratchRowBytes;
+    uint8_t* scr = s_scratch + ew * kGemmScrBytes;
+    uint64_t* bar_add = bar_addend + ew * 3;   // this warp's three addend boxes (EPI_TMA_ADD)
+    uint32_t add_ph = 0;
     for (int it = eg;; it += 2) {   // this group's tiles: it & 1 == eg
       const int acc = eg;
       const int qs = it % S::kTileQ;
@@ -531,11 +661,12 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
       float* bias_s = s_bias + (acc * 2 + ((it >> 1) & 1)) * BN;
       if (p.flags & EPI_BIAS)
         for (int i = et; i < BN; i += 128) bias_s[i] = (n0 + i < p.N) ? __ldg(p.bias + n0 + i) : 0.0f;
+      gemm_epilogue_prefetch_add(p, &map_add, bar_add, scr, lane, lane_q, batch, row0, n0);
       asm volatile("bar.sync %0, 128;" ::"r"(1 + eg) : "memory");
       mbar_wait(bar_tfull + acc, acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(lane_q * 32) << 16) + acc * BN;
-      const unsigned long long best = gemm_epilogue_tile<BN, S::kScratchRowBytes>(p, t_row, bias_s, scr, lane, lane_q, batch, row0, n0);
+      const unsigned long long best = gemm_epilogue_tile<BN>(p, &map_c, &map_add, bar_add, add_ph, t_row, bias_s, scr, lane, lane_q, batch, row0, n0);
       // accumulator fully read: hand it back to the MMA warp
       tc_fence_before();
       __syncwarp();
@@ -545,6 +676,8 @@ gemm_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
         if (r_batch < p.rows_per_batch) p.argmax_part[(long long)(batch * p.rows_per_batch + r_batch) * p.n_tiles_n + tn] = best;
       }
     }
+    // the copy engine has read (and written) this warp's last boxes before the CTA's shared memory goes away
+    if ((p.flags & EPI_TMA_C) && lane == 0) bulk_wait0();
   }
 
   tc_fence_before();
@@ -632,11 +765,10 @@ struct Gemm2Smem {
   static constexpr int kABytes = kGemmBM * kGemmBK * 2;      // this CTA's 128 rows of A: 16 KB
   static constexpr int kBBytes = (BN / 2) * kGemmBK * 2;     // this CTA's half of the W tile
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kScratchRowBytes = 128 + 16;
-  static constexpr int kScratchBytes = kGemmEpiGroups * 4 * 32 * kScratchRowBytes;
+  static constexpr int kScratchBytes = kGemmEpiGroups * 4 * kGemmScrBytes;
   static constexpr int kBiasBytes = 4 * BN * 4;
   static constexpr int kTileQ = 4;
-  static constexpr int kBarBytes = 512;
+  static constexpr int kBarBytes = 640;
   static constexpr int kFit = (232448 - 1024 - kScratchBytes - kBiasBytes - kBarBytes) / kStageBytes;
   static constexpr int kStages = kFit > 8 ? 8 : kFit;
   static constexpr int kTotal = kStages * kStageBytes + kScratchBytes + kBiasBytes + kBarBytes + 1024;
@@ -647,7 +779,8 @@ struct Gemm2Smem {
 template <int BN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm2_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
-                        GemmBf16Params p) {
+                        const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_add,
+    GemmBf16Params p) {
   using S = Gemm2Smem<BN>;
   extern __shared__ __align__(1024) uint8_t smem_dyn[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
@@ -662,7 +795,8 @@ gemm2_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
   uint64_t* bar_qempty = bar_qfull + S::kTileQ;    // [kTileQ]
   uint64_t* bar_ifull = bar_qempty + S::kTileQ;    // [kTileQ] peer: inbox entry written by the leader's producer
   uint64_t* bar_iempty = bar_ifull + S::kTileQ;    // [kTileQ] leader: inbox entry read by the peer's producer
-  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_iempty + S::kTileQ);
+  uint64_t* bar_addend = bar_iempty + S::kTileQ;   // [8 epilogue warps][3] addend boxes landed (EPI_TMA_ADD)
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_addend + 24);
   volatile int* s_tileq = reinterpret_cast<volatile int*>(s_tmem + 4);
   volatile int* s_inbox = s_tileq + S::kTileQ;
 
@@ -678,6 +812,8 @@ gemm2_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_w);
+    if (p.flags & EPI_TMA_C) tma_prefetch_desc(&map_c);
+    if (p.flags & EPI_TMA_ADD) tma_prefetch_desc(&map_add);
     for (int i = 0; i < 8; ++i) {
       mbar_init(bar_full + i, 1);
       mbar_init(bar_empty + i, 1);
@@ -692,6 +828,7 @@ gemm2_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       mbar_init(bar_ifull + i, 1);
       mbar_init(bar_iempty + i, 1);
     }
+    for (int i = 0; i < 24; ++i) mbar_init(bar_addend + i, 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -801,7 +938,9 @@ gemm2_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
     const int eg = ew >> 2;
     const int lane_q = warp & 3;
     const int et = (threadIdx.x - 64) & 127;
-    uint8_t* scr = s_scratch + ew * 32 * S::kScratchRowBytes;
+    uint8_t* scr = s_scratch + ew * kGemmScrBytes;
+    uint64_t* bar_add = bar_addend + ew * 3;   // this warp's three addend boxes (EPI_TMA_ADD)
+    uint32_t add_ph = 0;
     for (int it = eg;; it += 2) {
       const int acc = eg;
       const int qs = it % S::kTileQ;
@@ -817,11 +956,12 @@ gemm2_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       float* bias_s = s_bias + (acc * 2 + ((it >> 1) & 1)) * BN;
       if (p.flags & EPI_BIAS)
         for (int i = et; i < BN; i += 128) bias_s[i] = (n0 + i < p.N) ? __ldg(p.bias + n0 + i) : 0.0f;
+      gemm_epilogue_prefetch_add(p, &map_add, bar_add, scr, lane, lane_q, batch, row0, n0);
       asm volatile("bar.sync %0, 128;" ::"r"(1 + eg) : "memory");
       mbar_wait(bar_tfull + acc, acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(lane_q * 32) << 16) + acc * BN;
-      const unsigned long long best = gemm_epilogue_tile<BN, S::kScratchRowBytes>(p, t_row, bias_s, scr, lane, lane_q, batch, row0, n0);
+      const unsigned long long best = gemm_epilogue_tile<BN>(p, &map_c, &map_add, bar_add, add_ph, t_row, bias_s, scr, lane, lane_q, batch, row0, n0);
       // accumulator fully read: hand it back to the leader's MMA warp
       tc_fence_before();
       __syncwarp();
@@ -831,6 +971,8 @@ gemm2_bf16_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
         if (r_batch < p.rows_per_batch) p.argmax_part[(long long)(batch * p.rows_per_batch + r_batch) * p.n_tiles_n + tn] = best;
       }
     }
+    // the copy engine has read (and written) this warp's last boxes before the CTA's shared memory goes away
+    if ((p.flags & EPI_TMA_C) && lane == 0) bulk_wait0();
   }
 
   tc_fence_before();
