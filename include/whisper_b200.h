@@ -172,6 +172,21 @@ WT_API int wt_debug_gemm_ex(void* cuda_stream, const wt_debug_gemm_args* a);
 /* The encoder attention kernel alone: qkv [n_clips][S][3*H*64] bf16 (q | k | v) -> out [n_clips][S][H*64] bf16. */
 WT_API int wt_debug_attention_bf16(void* cuda_stream, const void* qkv, void* out, int n_clips, int S, int H);
 
+/* No-allocation entry point. It has no counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * ids_out[m] (int32, device) = index of the maximum of row m of A[M][K] . W[N][K]^T (+ bias[N], may be NULL), with the
+ * argmax rule of whisper.cpp:346-361 (last index among equal maxima; NaN only wins at index 0): the decoder's fused
+ * tied-logits + argmax product. A, W bf16 row-major device pointers, N and K multiples of 8. The call allocates
+ * nothing (no cudaMalloc / cudaFree, no allocating library routine): the GEMM's tile-scheduler words and its
+ * per-column-tile partial winners live in one static __device__ array of 1 MiB + 256 B that every GPU loading the
+ * library holds until exit. Limit: M * ceil(N / bn) <= 131072 partial winners (bn = 64 or 128 for M <= 128, else the
+ * largest of 256 / 192 / 128 dividing N) — e.g. 64 rows x 51 865 columns uses 26 048; beyond it the call fails with
+ * WT_ERR_INVALID and a message naming the limit. Asynchronous on cuda_stream. All calls share the scratch, which keeps
+ * the previous call's contents (the words that must start at zero are cleared on the stream first): calls that overlap
+ * on the GPU — different streams or host threads — race on it and must be serialised by the caller. */
+WT_API int wt_gemm_argmax_noalloc(void* cuda_stream, const void* A, const void* W, const float* bias, int M, int N,
+                                  int K, int32_t* ids_out);
+
 /* Debug / test hook: 64-bit order-independent digest of a device-resident buffer as the last call on this engine left
  * it, over the first n_clips clips. what: "mel_raw", "mel_tm", "conv1", "x", "qkv", "att", "hidden", "enc_out",
  * "cross_kv<layer>", "tokens". Equal bytes give equal digests: the bitwise-reproducibility tests compare these across

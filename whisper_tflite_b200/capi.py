@@ -30,7 +30,7 @@ EXPORTED = [
     "wt_get_step_logits", "wt_launch_count", "wt_last_error", "wt_version", "wt_debug_gemm_bf16",
     "wt_profile_enable", "wt_profile_read", "wt_stage_count", "wt_stage_name", "wt_debug_decoder_trace",
     "wt_set_decoder_group", "wt_debug_hash", "wt_debug_gemm_ex", "wt_debug_attention_bf16", "wt_log_mel_i16",
-    "wt_transcribe_tokens_i16",
+    "wt_transcribe_tokens_i16", "wt_gemm_argmax_noalloc",
 ]
 
 
@@ -275,6 +275,20 @@ def debug_gemm_ex(stream: int = 0, **kw):
         else:
             setattr(a, k, v)
     _check(load_library().wt_debug_gemm_ex(ctypes.c_void_p(stream), ctypes.byref(a)))
+
+
+NOALLOC_MAX_PARTIALS = 131072   # wt_gemm_argmax_noalloc: M * ceil(N / bn) partial winners its static device scratch holds
+
+
+def gemm_argmax_noalloc(a, w, bias, ids_out, stream: int = 0):
+    """wt_gemm_argmax_noalloc: ids_out[m] = argmax_n (a[m] . w[n] + bias[n]) with the reference's tie / NaN rule, on torch
+    CUDA tensors (a [M][K], w [N][K] bf16; bias [N] f32 or None; ids_out [M] int32). Allocates nothing on the device."""
+    M, K = a.shape
+    N = w.shape[0]
+    _check(load_library().wt_gemm_argmax_noalloc(
+        ctypes.c_void_p(stream), ctypes.c_void_p(a.data_ptr()), ctypes.c_void_p(w.data_ptr()),
+        ctypes.c_void_p(bias.data_ptr()) if bias is not None else None, M, N, K, ctypes.c_void_p(ids_out.data_ptr())))
+    return ids_out
 
 
 def debug_attention_bf16(qkv, out, n_heads: int, stream: int = 0):

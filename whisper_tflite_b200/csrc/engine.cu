@@ -17,6 +17,7 @@
 #include <cstdio>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <string>
 #include <tuple>
 #include <vector>
@@ -1602,3 +1603,140 @@ int wt_debug_attention_bf16(void* cuda_stream, const void* qkv, void* out, int n
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// wt_gemm_argmax_noalloc: the fused logits + argmax GEMM (EPI_ARGMAX, whisper.cpp:346-361's rule) for callers that may
+// not allocate — CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc. No counterpart in the
+// reference. Everything the kernels need besides the caller's operands —
+// the tile scheduler's two counters and the per-column-tile partial winners [M][ceil(N / bn)] — lives in ONE file-scope
+// device array of fixed size (every GPU that loads the library holds these kNoAllocScratchBytes until exit). In host
+// code the array's name is only a stand-in: its device address is taken once per device, with that device current,
+// through cudaGetSymbolAddress, and it is that pointer the kernels get.
+// All calls share the array and it keeps the last call's contents: the scheduler words are cleared on the caller's
+// stream before every launch, the partials in use are fully overwritten; calls that overlap on the GPU (two streams,
+// two host threads) race on it — serialise them.
+// ------------------------------------------------------------------------------------------------
+namespace {
+constexpr int kNoAllocHeaderBytes = 256;                    // scheduler counters (sched[0] next tile, sched[1] CTAs done)
+constexpr int kNoAllocMaxPartials = 131072;                 // u64 partial winners: M * ceil(N / bn) <= this (1 MiB)
+constexpr size_t kNoAllocScratchBytes = kNoAllocHeaderBytes + (size_t)kNoAllocMaxPartials * 8;
+constexpr int kNoAllocMaxDevices = 64;
+struct NoAllocDevice {
+  unsigned char* ptr = nullptr;   // device address of g_noalloc_scratch on this device
+  int num_sms = 0;
+};
+NoAllocDevice g_noalloc_dev[kNoAllocMaxDevices];
+std::mutex g_noalloc_mu;
+}  // namespace
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+namespace wt {
+// winner of each row out of its per-column-tile partials (packed (ordered value, index): one integer max)
+__global__ void __launch_bounds__(128) noalloc_argmax_rows_kernel(const unsigned long long* __restrict__ part, int n_part,
+                                                                   int* __restrict__ ids_out) {
+  __shared__ unsigned long long s_best[4];
+  const int m = blockIdx.x;
+  unsigned long long best = 0ull;
+  for (int i = threadIdx.x; i < n_part; i += 128) best = u64_max(best, part[(long long)m * n_part + i]);
+  best = warp_max_u64(best);
+  if ((threadIdx.x & 31) == 0) s_best[threadIdx.x >> 5] = best;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 4; ++w) best = u64_max(best, s_best[w]);
+    ids_out[m] = (int)(best & 0xffffffffull);
+  }
+}
+}  // namespace wt
+
+// once per device, with that device current: shared-memory attributes of the GEMM variants, SM count, scratch address
+static int noalloc_device_setup(int dev, NoAllocDevice** out) {
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return fail(WT_ERR_INVALID, "device %d outside [0, %d)", dev, kNoAllocMaxDevices);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  NoAllocDevice& nd = g_noalloc_dev[dev];
+  if (!nd.ptr) {
+    int major = 0, sms = 0;
+    WT_CUDA_OK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    WT_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (major != 10) return fail(WT_ERR_CUDA, "sm_100a only");
+    WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<64>::kTotal));
+    WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<128>::kTotal));
+    WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<192>::kTotal));
+    WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<256>::kTotal));
+    void* sym = nullptr;
+    WT_CUDA_OK(cudaGetSymbolAddress(&sym, g_noalloc_scratch));   // the array's address ON THE CURRENT DEVICE
+    if (!sym) return fail(WT_ERR_CUDA, "cudaGetSymbolAddress returned a null scratch address");
+    nd.num_sms = sms;
+    nd.ptr = (unsigned char*)sym;
+  }
+  *out = &nd;
+  return WT_OK;
+}
+
+template <int BN>
+static int noalloc_launch_gemm(const NoAllocDevice& nd, cudaStream_t st, const CUtensorMap& ma, const CUtensorMap& mw,
+                               wt::GemmBf16Params& p) {
+  using S = wt::GemmSmem<BN>;
+  const int n_tiles = p.tiles_per_batch * p.n_batches * p.n_tiles_n;
+  const int grid = n_tiles < nd.num_sms ? n_tiles : nd.num_sms;
+  wt::gemm_bf16_sm100_kernel<BN><<<grid, wt::kGemmThreads, S::kTotal, st>>>(ma, mw, ma, ma, p);   // no C / addend maps
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(WT_ERR_CUDA, "launch of gemm_bf16_sm100_kernel failed: %s", cudaGetErrorString(e));
+  return WT_OK;
+}
+
+extern "C" int wt_gemm_argmax_noalloc(void* cuda_stream, const void* A, const void* W, const float* bias, int M, int N,
+                                      int K, int32_t* ids_out) {
+  if (!A || !W || !ids_out || M < 1 || N < 8 || K < 8 || (K % 8) || (N % 8))
+    return fail(WT_ERR_INVALID, "bad GEMM arguments (M >= 1; N, K multiples of 8; A, W, ids_out device pointers)");
+  const int bn = pick_bn(M, N);
+  const int n_tiles_n = (N + bn - 1) / bn;
+  if ((long long)M * n_tiles_n > kNoAllocMaxPartials)
+    return fail(WT_ERR_INVALID,
+                "wt_gemm_argmax_noalloc: M * ceil(N / %d) = %lld partial winners exceed the static scratch of %d (%zu bytes); "
+                "use the engine's allocating path for this size",
+                bn, (long long)M * n_tiles_n, kNoAllocMaxPartials, kNoAllocScratchBytes);
+  int dev = 0;
+  WT_CUDA_OK(cudaGetDevice(&dev));
+  NoAllocDevice* nd = nullptr;
+  WT_TRY(noalloc_device_setup(dev, &nd));
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  CUtensorMap ma, mw;
+  {
+    const uint64_t ad[3] = {(uint64_t)K, (uint64_t)M, 1}, as[2] = {(uint64_t)K * 2, (uint64_t)K * 2 * (uint64_t)M};
+    const uint32_t abox[3] = {64, 128, 1};
+    WT_TRY(make_map_bf16(&ma, A, 3, ad, as, abox));
+    const uint64_t wd[2] = {(uint64_t)K, (uint64_t)N}, ws[1] = {(uint64_t)K * 2};
+    const uint32_t wbox[2] = {64, (uint32_t)bn};
+    WT_TRY(make_map_bf16(&mw, W, 2, wd, ws, wbox));
+  }
+  wt::GemmBf16Params p{};
+  p.bias = bias;
+  p.argmax_part = reinterpret_cast<unsigned long long*>(nd->ptr + kNoAllocHeaderBytes);
+  p.sched = reinterpret_cast<int*>(nd->ptr);
+  p.cmap = RowMap{0, M, N};
+  p.add_map = RowMap{0, 1, 0};
+  p.M = M;
+  p.N = N;
+  p.K = K;
+  p.rows_per_batch = M;
+  p.tiles_per_batch = (M + 127) / 128;
+  p.n_batches = 1;
+  p.n_tiles_n = n_tiles_n;
+  p.flags = wt::EPI_ARGMAX | (bias ? wt::EPI_BIAS : 0);
+  p.taps = 1;
+  p.kblocks_per_tap = (K + 63) / 64;
+  // the scheduler words must start at zero whatever an earlier (possibly failed) call left there
+  WT_CUDA_OK(cudaMemsetAsync(nd->ptr, 0, kNoAllocHeaderBytes, st));
+  switch (bn) {
+    case 64: WT_TRY(noalloc_launch_gemm<64>(*nd, st, ma, mw, p)); break;
+    case 128: WT_TRY(noalloc_launch_gemm<128>(*nd, st, ma, mw, p)); break;
+    case 192: WT_TRY(noalloc_launch_gemm<192>(*nd, st, ma, mw, p)); break;
+    case 256: WT_TRY(noalloc_launch_gemm<256>(*nd, st, ma, mw, p)); break;
+    default: return fail(WT_ERR_INVALID, "bad BN %d", bn);
+  }
+  wt::noalloc_argmax_rows_kernel<<<M, 128, 0, st>>>(p.argmax_part, n_tiles_n, ids_out);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(WT_ERR_CUDA, "launch of noalloc_argmax_rows_kernel failed: %s", cudaGetErrorString(e));
+  return WT_OK;
+}
