@@ -28,6 +28,7 @@
 #include "attn3_sm100.cuh"
 #include "decoder_stream_sm100.cuh"
 #include "gemm_sm100.cuh"
+#include "gemm_lean_sm100.cuh"
 #include "mel_host.h"
 #include "mel_kernels.cuh"
 #include "simt_kernels.cuh"
@@ -404,6 +405,20 @@ static int launch_gemm_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMap
   return e->check_launch("gemm_bf16_sm100_kernel");
 }
 
+// sixteen-epilogue-warp kernel (gemm_lean_sm100.cuh): plain bf16 C through TMA, bias / GELU / TMA residual only
+template <int BN>
+static int launch_gemm_lean_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mc, const CUtensorMap& mr, wt::GemmBf16Params& p) {
+  using S = wt::GemmLeanSmem<BN>;
+  p.n_tiles_n = (p.N + BN - 1) / BN;
+  const int n_tiles = p.tiles_per_batch * p.n_batches * p.n_tiles_n;
+  const int grid = n_tiles < e->num_sms ? n_tiles : e->num_sms;
+  if (!e->gemm_sched) return fail(WT_ERR_STATE, "GEMM tile scheduler not allocated (engine not initialised)");
+  p.sched = e->gemm_sched;
+  e->pre_launch();
+  wt::gemm_lean_sm100_kernel<BN><<<grid, wt::kLeanThreads, S::total((p.flags & wt::EPI_TMA_ADD) != 0), e->stream>>>(ma, mw, mc, mr, p);
+  return e->check_launch("gemm_lean_sm100_kernel");
+}
+
 // CTA-pair kernel (gemm2_bf16_sm100_kernel): 256-row tiles on a cluster of two CTAs
 template <int BN>
 static int launch_gemm2_bn(wt_engine* e, const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mc, const CUtensorMap& mr, wt::GemmBf16Params& p) {
@@ -486,6 +501,7 @@ int wt_engine::gemm_bf16(const void* A, const uint64_t* a_dims, const uint64_t* 
   // has such a map as well (EPI_TMA_ADD: the residual GEMMs) both directions go through 32 x 32 boxes, the addend
   // prefetched by the copy engine a chunk ahead and updated in place in shared memory.
   CUtensorMap mc = ma, mr = ma;
+  bool lean = false;
   {
     static const char* ov = getenv("WT_GEMM_TMA_C");   // "0": the epilogue warps load / store themselves; "1": no TMA addend
     auto as_tensor = [&](const void* base, const RowMap& m, long long& bstride) {
@@ -499,9 +515,13 @@ int wt_engine::gemm_bf16(const void* A, const uint64_t* a_dims, const uint64_t* 
     long long cb = 0, rb = 0;
     if (plain_out && as_tensor(C, cmap, cb) && L.N >= 64 && bn >= 64 && !(ov && ov[0] == '0')) {
       const bool tma_add = (flags & wt::EPI_ADD) && as_tensor(addend, add_map, rb) && !(ov && ov[0] == '1');
+      // the sixteen-epilogue-warp kernel: everything it needs goes through TMA (32-column boxes in both directions)
+      static const char* ovl = getenv("WT_GEMM_LEAN");   // "0": never (A/B measurements)
+      lean = !pair && !force_bn && bn >= 128 && L.N % bn == 0 && M >= 1024 && (tma_add || !(flags & wt::EPI_ADD)) &&
+             !(ovl && ovl[0] == '0');
       const uint64_t cdims[3] = {(uint64_t)L.N, (uint64_t)rows_per_batch, (uint64_t)n_batches};
       const uint64_t cstr[2] = {(uint64_t)cmap.row_stride * 2, (uint64_t)cb * 2};
-      const uint32_t cbox[3] = {tma_add ? 32u : 64u, 32, 1};
+      const uint32_t cbox[3] = {(tma_add || lean) ? 32u : 64u, 32, 1};
       WT_TRY(get_map(&mc, C, 3, cdims, cstr, cbox));
       p.flags |= wt::EPI_TMA_C;
       if (tma_add) {
@@ -509,6 +529,13 @@ int wt_engine::gemm_bf16(const void* A, const uint64_t* a_dims, const uint64_t* 
         WT_TRY(get_map(&mr, addend, 3, cdims, rstr, cbox));
         p.flags |= wt::EPI_TMA_ADD;
       }
+    }
+  }
+  if (lean) {
+    switch (bn) {
+      case 128: return launch_gemm_lean_bn<128>(this, ma, mw, mc, mr, p);
+      case 192: return launch_gemm_lean_bn<192>(this, ma, mw, mc, mr, p);
+      case 256: return launch_gemm_lean_bn<256>(this, ma, mw, mc, mr, p);
     }
   }
   if (pair) {
@@ -615,6 +642,9 @@ int wt_engine::init_kernels() {
   WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<128>::kTotal));
   WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<192>::kTotal));
   WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_bf16_sm100_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::GemmSmem<256>::kTotal));
+  WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_lean_sm100_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (wt::GemmLeanSmem<128>::total(false) > wt::GemmLeanSmem<128>::total(true) ? wt::GemmLeanSmem<128>::total(false) : wt::GemmLeanSmem<128>::total(true))));
+  WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_lean_sm100_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, (wt::GemmLeanSmem<192>::total(false) > wt::GemmLeanSmem<192>::total(true) ? wt::GemmLeanSmem<192>::total(false) : wt::GemmLeanSmem<192>::total(true))));
+  WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm_lean_sm100_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (wt::GemmLeanSmem<256>::total(false) > wt::GemmLeanSmem<256>::total(true) ? wt::GemmLeanSmem<256>::total(false) : wt::GemmLeanSmem<256>::total(true))));
   WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm2_bf16_sm100_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::Gemm2Smem<128>::kTotal));
   WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm2_bf16_sm100_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::Gemm2Smem<192>::kTotal));
   WT_CUDA_OK(cudaFuncSetAttribute(wt::gemm2_bf16_sm100_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, wt::Gemm2Smem<256>::kTotal));
