@@ -232,8 +232,14 @@ def run_gpu(args, cfg_name, B):
 
     # Serving arrangement (capi.EnginePool): N engines per GPU on separate streams, batches alternate between them, so
     # one batch's greedy decoder (latency-bound, a few thread-block clusters) runs underneath the next batches' mel +
-    # encoder. Decoder clusters of 8 CTAs (wt_config.decoder_cluster) hold 16 clips on 8 SMs instead of 16: a batch's
-    # decoder takes longer but fewer SM-milliseconds, and five engines keep enough batches in flight.
+    # encoder. Small decoder clusters (wt_config.decoder_cluster) hold 16 clips on 4 or 8 SMs instead of 16: a batch's
+    # decoder takes longer but fewer SM-milliseconds, and more engines keep enough batches in flight. Defaults from the
+    # r02j sweep: whisper-tiny 8 engines x 4-CTA clusters (7.83 ms per step against 8.09 for 5 x 8
+    # at the same clock); wider models 5 x 8 (a 4-CTA cluster cannot hold 16 clips x 8+ heads of cross-attention pairs).
+    if args.engines <= 0:
+        args.engines = 8 if dims.n_heads <= 6 else 5
+    if args.dec_cluster <= 0:
+        args.dec_cluster = 4 if dims.n_heads <= 6 else 8
     n_eng = max(1, args.engines)
     # activations + cross-K/V streams of one engine (bytes); the pool must fit well inside 180 GB
     per_engine = B * (1500 * dims.d_model * 2 * 11 + 3002 * (dims.d_model + 80) * 2 + 480000 * 4 + 80 * 3000 * 8 +
@@ -488,9 +494,11 @@ def main():
     ap.add_argument("--clips", type=int, default=0, help="clips per batch and GPU (0 = the configuration's)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--dec-group", type=int, default=16, help="clips per decoder cluster when engines > 1")
-    ap.add_argument("--dec-cluster", type=int, default=8,
-                    help="CTAs per decoder cluster when engines > 1 (8: 16 clips on 8 SMs; 16: lowest latency per batch)")
-    ap.add_argument("--engines", type=int, default=5, help="engines per GPU that batches alternate between (1 = no pipelining)")
+    ap.add_argument("--dec-cluster", type=int, default=0,
+                    help="CTAs per decoder cluster when engines > 1 (0 = per model: 4 for whisper-tiny, else 8; 16: lowest "
+                         "latency per batch)")
+    ap.add_argument("--engines", type=int, default=0,
+                    help="engines per GPU that batches alternate between (0 = per model: 8 for whisper-tiny, else 5; 1 = no pipelining)")
     args = ap.parse_args()
     cfg = CONFIGS[args.config]
     MODEL = cfg["model"]

@@ -254,3 +254,28 @@ def test_nan_logit_never_wins_unless_first(nan_row, oracle_built, filters):
     assert model_ref.argmax_last(row) == 3
     row[0] = np.nan
     assert model_ref.argmax_last(row) == 0
+
+
+def test_decoder_cluster_sizes_give_identical_tokens():
+    """The pool's decoder arrangement (wt_config.decoder_cluster = 4 or 8 CTAs per 16-clip group, bench.py's default for
+    the serving pool) against the single-call default (16-CTA clusters, the batch spread over every co-resident cluster):
+    which CTA owns a column slice or a (clip, head) pair changes, the arithmetic per element does not — ids, lens and the
+    step-0 logits are bit-identical, with a ragged last group (40 clips = 16 + 16 + 8)."""
+    from whisper_tflite_b200 import capi
+    path, dims, W = weight_file("tiny")
+    n = 40
+    pcm = synth.synth_pcm(n, seed=21)
+    ref = None
+    for cluster, group in ((0, 0), (16, 16), (8, 16), (4, 16), (4, 8)):
+        eng = capi.Engine(path, max_batch=n, decoder_cluster=cluster, keep_logits=True)
+        eng.set_decoder_group(group)
+        ids, lens = eng.transcribe_tokens(pcm)
+        lg = eng.step_logits(0, n).copy()
+        eng.close()
+        if ref is None:
+            ref = (ids.copy(), lens.copy(), lg)
+            assert (lens >= 5).all()
+            continue
+        np.testing.assert_array_equal(ids, ref[0], err_msg=f"cluster {cluster} group {group}")
+        np.testing.assert_array_equal(lens, ref[1])
+        np.testing.assert_array_equal(lg, ref[2])

@@ -172,8 +172,9 @@ EncodeTiledFn get_encode_tiled() {
 // bf16 tensor; inner box 64 elements with the 128B swizzle, or 32 elements with the 64B swizzle. dims/strides innermost
 // first; strides in bytes for dims 1..rank-1.
 int make_map_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                  const uint32_t* box) {
-  const CUtensorMapSwizzle swz = box[0] == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
+                  const uint32_t* box, bool no_swizzle = false) {
+  const CUtensorMapSwizzle swz = no_swizzle ? CU_TENSOR_MAP_SWIZZLE_NONE
+                                            : (box[0] == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B);
   EncodeTiledFn fn = get_encode_tiled();
   if (!fn) return fail(WT_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
   cuuint64_t gd[5];
@@ -415,7 +416,7 @@ static int launch_gemm_lean_bn(wt_engine* e, const CUtensorMap& ma, const CUtens
   if (!e->gemm_sched) return fail(WT_ERR_STATE, "GEMM tile scheduler not allocated (engine not initialised)");
   p.sched = e->gemm_sched;
   e->pre_launch();
-  wt::gemm_lean_sm100_kernel<BN><<<grid, wt::kLeanThreads, S::total((p.flags & wt::EPI_TMA_ADD) != 0), e->stream>>>(ma, mw, mc, mr, p);
+  wt::gemm_lean_sm100_kernel<BN><<<grid, wt::kLeanThreads, S::total((p.flags & (wt::EPI_TMA_ADD | wt::EPI_SPLIT_KV)) != 0), e->stream>>>(ma, mw, mc, mr, p);
   return e->check_launch("gemm_lean_sm100_kernel");
 }
 
@@ -503,6 +504,21 @@ int wt_engine::gemm_bf16(const void* A, const uint64_t* a_dims, const uint64_t* 
   CUtensorMap mc = ma, mr = ma;
   bool lean = false;
   {
+    // The decoder's K/V stream through TMA (sixteen-epilogue-warp kernel): [pair][chunk][K | V][128 keys][64] as a 5-D tensor
+    // WITHOUT swizzle — the warps write their box with the 16-byte pieces XOR-ed by (key & 7), which is exactly the
+    // stream's layout (decoder_stream_sm100.cuh reads it with ldmatrix) once the copy engine moves the box verbatim
+    static const char* ovk = getenv("WT_GEMM_LEAN");
+    if ((flags & wt::EPI_SPLIT_KV) && next_kv_chunked && rows_per_batch == dims.n_audio_ctx && !pair && !force_bn &&
+        (bn == 256 || bn == 128) && L.N == 2 * dims.n_heads * 64 && L.N % bn == 0 && !(ovk && ovk[0] == '0')) {
+      const uint64_t cpp = (uint64_t)p.kv_cpp;
+      const uint64_t kd[5] = {64, 128, 2, cpp, (uint64_t)n_batches * dims.n_heads};
+      const uint64_t ks[4] = {128, 128 * 128, 2 * 128 * 128, cpp * 2 * 128 * 128};
+      const uint32_t kbox[5] = {64, 32, 1, 1, 1};
+      WT_TRY(make_map_bf16(&mc, next_kv_k, 5, kd, ks, kbox, true));
+      lean = true;
+    }
+  }
+  if (!lean) {
     static const char* ov = getenv("WT_GEMM_TMA_C");   // "0": the epilogue warps load / store themselves; "1": no TMA addend
     auto as_tensor = [&](const void* base, const RowMap& m, long long& bstride) {
       bstride = -1;

@@ -32,6 +32,7 @@ struct GemmLeanSmem {
   static constexpr int kTileQ = 4;
   static constexpr int kBarBytes = 1024;
   static constexpr int kMaxStages = 6;
+  // `add`: residual GEMM (EPI_TMA_ADD) or the K/V-stream scatter (EPI_SPLIT_KV: one 4 KB box of 32 keys x 128 bytes)
   __host__ __device__ static constexpr int boxes(bool add) { return add ? (BN <= 192 ? 3 : 2) : 1; }
   __host__ __device__ static constexpr int stages(bool add) {
     const int fit = (232448 - 1024 - kLeanEpiWarps * boxes(add) * 2048 - kBarBytes) / kStageBytes;
@@ -48,6 +49,69 @@ struct GemmLeanSmem {
 // t_row / bias_s already point at column col0. Boxes: chunk c of a tile with an addend sits in box c % kBoxes (the first
 // kBoxes - 1 were requested by the caller before the accumulator was waited for); without one the rotation carries on
 // across tiles in `rot`, so "all but the last kBoxes - 1 stores have been read" always frees the box about to be written.
+__device__ __forceinline__ void tma_store_5d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2, int c3, int c4) {
+  asm volatile("cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+               : "memory");
+}
+
+// The cross-attention K/V projection's epilogue (EPI_SPLIT_KV, streaming layout): the tile's 128 rows are one 128-key
+// chunk of clip `batch`, a 64-column block is one head's K or V. A lane writes its key's 128-byte row into the warp's
+// 4 KB box with the 16-byte pieces XOR-ed by (key & 7) — the layout the decoder's ldmatrix reads (gemm_sm100.cuh's
+// scatter writes the same bytes with 16-byte global stores) — and the box goes out verbatim (tensor map without swizzle)
+// to [pair][chunk][K | V][32 keys of this warp]. Keys past the clip's end are written as zeros.
+template <int kChunks>
+__device__ __forceinline__ void gemm_lean_epilogue_kv(const GemmBf16Params& p, const CUtensorMap* map_kv, uint32_t t_row,
+                                                      uint8_t* scr, int lane, int lane_q, int batch, int row0, int ncol0) {
+  static_assert(kChunks % 2 == 0, "whole 64-column blocks per warp");
+  const bool row_ok = row0 + lane_q * 32 + lane < p.rows_per_batch;
+  uint8_t* row = scr + lane * 128;
+  const int sw = lane & 7;
+#pragma unroll 1
+  for (int c = 0; c < kChunks; ++c) {
+    uint32_t v[32];
+    tmem_ld32(t_row + c * 32, v);
+    tmem_ld_wait();
+    if (p.flags & EPI_BIAS) {
+      const float4* bg = reinterpret_cast<const float4*>(p.bias + ncol0 + c * 32);
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        const float4 b4 = __ldg(bg + (j >> 2));
+        v[j] = __float_as_uint(__uint_as_float(v[j]) + b4.x);
+        v[j + 1] = __float_as_uint(__uint_as_float(v[j + 1]) + b4.y);
+        v[j + 2] = __float_as_uint(__uint_as_float(v[j + 2]) + b4.z);
+        v[j + 3] = __float_as_uint(__uint_as_float(v[j + 3]) + b4.w);
+      }
+    }
+    const int half4 = (c & 1) << 2;
+    if (half4 == 0) {
+      if (lane == 0) bulk_wait_read0();   // the previous block's store has read the box
+      __syncwarp();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint4 o = make_uint4(0u, 0u, 0u, 0u);
+      if (row_ok)
+        o = make_uint4(pack_bf16x2(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1])),
+                       pack_bf16x2(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3])),
+                       pack_bf16x2(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5])),
+                       pack_bf16x2(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7])));
+      *reinterpret_cast<uint4*>(row + (((half4 + i) ^ sw) << 4)) = o;
+    }
+    if (half4 != 0) {
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) {
+        const int cb = (ncol0 + (c - 1) * 32) >> 6;
+        const int which = cb >= p.kv_H ? 1 : 0;
+        tma_store_5d(map_kv, scr, 0, lane_q * 32, which, row0 >> 7, batch * p.kv_H + (cb - which * p.kv_H));
+        bulk_commit();
+      }
+    }
+  }
+}
+
 template <int kChunks>
 __device__ __forceinline__ void gemm_lean_epilogue(const GemmBf16Params& p, const CUtensorMap* map_c, const CUtensorMap* map_add,
                                                    uint64_t* bar_add, uint32_t& add_ph, int& rot, uint32_t t_row, int kBoxes,
@@ -131,7 +195,8 @@ gemm_lean_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
   extern __shared__ __align__(1024) uint8_t smem_dyn[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
   const bool has_add = (p.flags & EPI_TMA_ADD) != 0;
-  const int n_stages = S::stages(has_add), n_boxes = S::boxes(has_add);
+  const bool has_kv = (p.flags & EPI_SPLIT_KV) != 0;   // two 2 KB boxes = the one 4 KB box of the K/V epilogue (BN = 256 / 128)
+  const int n_stages = S::stages(has_add || has_kv), n_boxes = has_kv ? 2 : S::boxes(has_add);
   uint8_t* s_stage = smem;
   uint8_t* s_scratch = s_stage + n_stages * S::kStageBytes;
   uint64_t* bar_full = reinterpret_cast<uint64_t*>(s_scratch + kLeanEpiWarps * n_boxes * 2048);
@@ -286,7 +351,11 @@ gemm_lean_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
       mbar_wait(bar_tfull + acc, acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(lane_q * 32) << 16) + acc * BN + half * kHalf;
-      gemm_lean_epilogue<kChunks>(p, &map_c, &map_add, bar_add, add_ph, rot, t_row, n_boxes, scr, lane, rowq, batch, ncol0);
+      if (has_kv) {
+        if constexpr (kChunks % 2 == 0) gemm_lean_epilogue_kv<kChunks>(p, &map_c, t_row, scr, lane, lane_q, batch, row0, ncol0);
+      } else {
+        gemm_lean_epilogue<kChunks>(p, &map_c, &map_add, bar_add, add_ph, rot, t_row, n_boxes, scr, lane, rowq, batch, ncol0);
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + acc);
