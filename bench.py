@@ -232,14 +232,15 @@ def run_gpu(args, cfg_name, B):
 
     # Serving arrangement (capi.EnginePool): N engines per GPU on separate streams, batches alternate between them, so
     # one batch's greedy decoder (latency-bound, a few thread-block clusters) runs underneath the next batches' mel +
-    # encoder. Small decoder clusters (wt_config.decoder_cluster) hold 16 clips on 4 or 8 SMs instead of 16: a batch's
-    # decoder takes longer but fewer SM-milliseconds, and more engines keep enough batches in flight. Defaults from the
-    # r02j sweep: whisper-tiny 8 engines x 4-CTA clusters (7.83 ms per step against 8.09 for 5 x 8
-    # at the same clock); wider models 5 x 8 (a 4-CTA cluster cannot hold 16 clips x 8+ heads of cross-attention pairs).
+    # encoder. Decoder clusters of 8 CTAs (wt_config.decoder_cluster) hold 16 clips on 8 SMs instead of 16: a batch's
+    # decoder takes longer but fewer SM-milliseconds, and five engines keep enough batches in flight. r02j sweeps
+    # (DESIGN.md section 7): 8 engines x 4-CTA clusters is 0-3 % faster on one GPU (7.74-7.83 against 7.98-8.09 ms on one
+    # box, 8.06 against 8.07 on another) but 2 % slower device-resident and 8 % slower end to end with eight ranks on one
+    # host (64 engine threads on 32 cores), so the default stays 5 x 8 for every N; --engines 8 --dec-cluster 4 selects it.
     if args.engines <= 0:
-        args.engines = 8 if dims.n_heads <= 6 else 5
+        args.engines = 5
     if args.dec_cluster <= 0:
-        args.dec_cluster = 4 if dims.n_heads <= 6 else 8
+        args.dec_cluster = 8
     n_eng = max(1, args.engines)
     # activations + cross-K/V streams of one engine (bytes); the pool must fit well inside 180 GB
     per_engine = B * (1500 * dims.d_model * 2 * 11 + 3002 * (dims.d_model + 80) * 2 + 480000 * 4 + 80 * 3000 * 8 +
@@ -495,10 +496,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--dec-group", type=int, default=16, help="clips per decoder cluster when engines > 1")
     ap.add_argument("--dec-cluster", type=int, default=0,
-                    help="CTAs per decoder cluster when engines > 1 (0 = per model: 4 for whisper-tiny, else 8; 16: lowest "
-                         "latency per batch)")
+                    help="CTAs per decoder cluster when engines > 1 (0 = 8; 4 needs <= 6 heads; 16: lowest latency per batch)")
     ap.add_argument("--engines", type=int, default=0,
-                    help="engines per GPU that batches alternate between (0 = per model: 8 for whisper-tiny, else 5; 1 = no pipelining)")
+                    help="engines per GPU that batches alternate between (0 = 5; 1 = no pipelining)")
     args = ap.parse_args()
     cfg = CONFIGS[args.config]
     MODEL = cfg["model"]
