@@ -292,7 +292,7 @@ def gemm_argmax_noalloc(a, w, bias, ids_out, stream: int = 0):
 
 
 def debug_attention_bf16(qkv, out, n_heads: int, stream: int = 0):
-    """attention2_sm100_kernel on qkv [B][S][3*H*64] -> out [B][S][H*64] (torch CUDA bf16 tensors)."""
+    """attention3_sm100_kernel on qkv [B][S][3*H*64] -> out [B][S][H*64] (torch CUDA bf16 tensors)."""
     B, S, _ = qkv.shape
     _check(load_library().wt_debug_attention_bf16(ctypes.c_void_p(stream), ctypes.c_void_p(qkv.data_ptr()),
                                                   ctypes.c_void_p(out.data_ptr()), B, S, n_heads))
