@@ -30,8 +30,8 @@ namespace wt {
 constexpr int kAt3Threads = 64 + 256;   // TMA warp, MMA warp, 2 softmax warpgroups (one per query tile)
 constexpr int kAt3Stages = 4;
 struct Attn3Smem {
-  static constexpr int kQ = 0;                                   // Q0, Q1: 2 x 16 KB
-  static constexpr int kKV = kQ + 2 * kAtTile;                   // kAt3Stages x (K tile + V tile)
+  static constexpr int kQ = 0;                                   // 2 buffers x (Q0, Q1): 4 x 16 KB (this item's, the next item's)
+  static constexpr int kKV = kQ + 4 * kAtTile;                   // kAt3Stages x (K tile + V tile)
   static constexpr int kBars = kKV + kAt3Stages * 2 * kAtTile;
   static constexpr int kTotal = kBars + 256 + 1024;              // + alignment slack
 };
@@ -180,29 +180,39 @@ __device__ __forceinline__ void at3_rescale_o(uint32_t t_o, float alpha) {
   }
 }
 
-// grid = (ceil(S/256), H, B); block = 320
+// Persistent: grid = min(items, SMs) CTAs, item = (clip, head, 256-query pair), drawn from a global counter one ahead
+// (sched[0] next item, sched[1] CTAs done; the last CTA out re-arms both — the GEMM kernels' protocol and counters: the
+// launches of a stream are serialised). A launch that shares the GPU with other engines' decoders needs no second wave of
+// CTAs, the K/V ring and the next item's Q tiles keep loading across item boundaries, and tensor memory, barriers and
+// the descriptor prefetch are set up once per SM instead of 15 times. block = 320.
 __global__ void __launch_bounds__(kAt3Threads, 1)
-attention3_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restrict__ out, int S, int H) {
+attention3_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restrict__ out, int S, int H, int B,
+                        int* __restrict__ sched) {
   extern __shared__ __align__(1024) uint8_t smem_dyn[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Attn3Smem::kBars);
-  uint64_t* bar_q = bars;                              // 1
-  uint64_t* bar_kv_full = bars + 1;                    // kAt3Stages
+  uint64_t* bar_q_full = bars;                         // [2] Q buffer loaded + item index published (end marker: plain arrive)
+  uint64_t* bar_q_empty = bars + 2;                    // [2] 9 arrivals: the item's last S product retired + 8 softmax warps
+  uint64_t* bar_kv_full = bars + 4;                    // kAt3Stages
   uint64_t* bar_kv_empty = bar_kv_full + kAt3Stages;   // kAt3Stages
   uint64_t* bar_s_full = bar_kv_empty + kAt3Stages;    // [2] per query tile, phase = j & 1
   uint64_t* bar_p_full = bar_s_full + 2;               // [2] (4 arrivals: one per softmax warp of the tile)
   uint64_t* bar_o_done = bar_p_full + 2;               // [2] PV_w,j complete
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_o_done + 2);
+  volatile int* s_item = reinterpret_cast<volatile int*>(s_tmem + 2);   // [2]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int qp = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int D = H * 64;
-  const int q0 = qp * 256;
   const int nkb = (S + 127) / 128;
+  const int n_qp = (S + 255) / 256;
+  const int n_items = B * H * n_qp;   // item = (b * H + h) * n_qp + qp: the 6 items of a (clip, head) run on neighbouring CTAs
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_qkv);
-    mbar_init(bar_q, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar_q_full + i, 1);
+      mbar_init(bar_q_empty + i, 9);
+    }
     for (int i = 0; i < kAt3Stages; ++i) {
       mbar_init(bar_kv_full + i, 1);
       mbar_init(bar_kv_empty + i, 1);
@@ -224,61 +234,87 @@ attention3_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat
 
   if (warp == 0) {
     if (lane == 0) {
-      mbar_expect_tx(bar_q, 2 * kAtTile);
-      tma_load_3d(smem + Attn3Smem::kQ, &map_qkv, bar_q, h * 64, q0, b);
-      tma_load_3d(smem + Attn3Smem::kQ + kAtTile, &map_qkv, bar_q, h * 64, q0 + 128, b);
       int stage = 0;
       uint32_t phase = 0;
-      for (int j = 0; j < nkb; ++j) {
-        mbar_wait(bar_kv_empty + stage, phase ^ 1);
-        uint8_t* sk = smem + Attn3Smem::kKV + stage * 2 * kAtTile;
-        mbar_expect_tx(bar_kv_full + stage, 2 * kAtTile);
-        tma_load_3d(sk, &map_qkv, bar_kv_full + stage, D + h * 64, j * 128, b);
-        tma_load_3d(sk + kAtTile, &map_qkv, bar_kv_full + stage, 2 * D + h * 64, j * 128, b);
-        if (++stage == kAt3Stages) { stage = 0; phase ^= 1; }
+      int next_item = (int)blockIdx.x;
+      for (int it = 0;; ++it) {
+        const int item = next_item < n_items ? next_item : -1;
+        if (item >= 0) next_item = (int)gridDim.x + atomicAdd(sched, 1);
+        const int qb = it & 1;
+        mbar_wait(bar_q_empty + qb, (uint32_t)((it >> 1) & 1) ^ 1u);   // item it - 2 is done with this Q buffer and slot
+        s_item[qb] = item;
+        if (item < 0) {
+          mbar_arrive(bar_q_full + qb);
+          break;
+        }
+        const int qp = item % n_qp, bh = item / n_qp, h = bh % H, b = bh / H;
+        uint8_t* sq = smem + Attn3Smem::kQ + qb * 2 * kAtTile;
+        mbar_expect_tx(bar_q_full + qb, 2 * kAtTile);
+        tma_load_3d(sq, &map_qkv, bar_q_full + qb, h * 64, qp * 256, b);
+        tma_load_3d(sq + kAtTile, &map_qkv, bar_q_full + qb, h * 64, qp * 256 + 128, b);
+        for (int j = 0; j < nkb; ++j) {
+          mbar_wait(bar_kv_empty + stage, phase ^ 1);
+          uint8_t* sk = smem + Attn3Smem::kKV + stage * 2 * kAtTile;
+          mbar_expect_tx(bar_kv_full + stage, 2 * kAtTile);
+          tma_load_3d(sk, &map_qkv, bar_kv_full + stage, D + h * 64, j * 128, b);
+          tma_load_3d(sk + kAtTile, &map_qkv, bar_kv_full + stage, 2 * D + h * 64, j * 128, b);
+          if (++stage == kAt3Stages) { stage = 0; phase ^= 1; }
+        }
+      }
+      __threadfence();
+      if (atomicAdd(sched + 1, 1) == (int)gridDim.x - 1) {   // last CTA out re-arms the counters for the next launch
+        sched[0] = 0;
+        sched[1] = 0;
+        __threadfence();
       }
     }
   } else if (warp == 1) {
     constexpr uint32_t idesc_s = make_idesc_bf16(128, 128);
     constexpr uint32_t idesc_o = make_idesc_bf16(128, 64) | (1u << 16);  // B (= V) is MN-major
-    const uint32_t q_addr = smem_u32(smem + Attn3Smem::kQ);
-    auto issue_s = [&](int w, int j) {   // S_w,j = Q_w K_j^T  (the caller has waited for K_j)
-      if (elect_one()) {
-        const int stage = j % kAt3Stages;
-        const uint64_t da = make_sw128_desc(q_addr + w * kAtTile);
-        const uint64_t db = make_sw128_desc(smem_u32(smem + Attn3Smem::kKV + stage * 2 * kAtTile));
-#pragma unroll
-        for (int k = 0; k < 4; ++k) umma_bf16(tmem_s + w * 128, da + 2 * k, db + 2 * k, idesc_s, k != 0 ? 1u : 0u);
-        umma_commit(bar_s_full + w);
-      }
-      __syncwarp();
-    };
-    mbar_wait(bar_q, 0);
-    mbar_wait(bar_kv_full + 0, 0);
-    tc_fence_after();
-    issue_s(0, 0);
-    issue_s(1, 0);
-    for (int j = 0; j < nkb; ++j) {
-      const int stage = j % kAt3Stages;
-      if (j + 1 < nkb) {   // K_j+1 (and V_j+1) landed: both query tiles' next S products need it
-        mbar_wait(bar_kv_full + (j + 1) % kAt3Stages, (uint32_t)(((j + 1) / kAt3Stages) & 1));
-      }
-      for (int w = 0; w < 2; ++w) {
-        mbar_wait(bar_p_full + w, (uint32_t)(j & 1));   // P_w,j is in tensor memory, so S_w,j has been read
-        tc_fence_after();
-        if (j + 1 < nkb) issue_s(w, j + 1);             // ahead of PV_w,j: the softmax warps restart one MMA earlier
+    uint32_t g = 0;   // key blocks processed by this CTA so far: ring stage g % kAt3Stages, barrier parities from g
+    for (int it = 0;; ++it) {
+      const int qb = it & 1;
+      mbar_wait(bar_q_full + qb, (uint32_t)((it >> 1) & 1));
+      if (s_item[qb] < 0) break;
+      const uint32_t q_addr = smem_u32(smem + Attn3Smem::kQ + qb * 2 * kAtTile);
+      auto issue_s = [&](int w, uint32_t gi, bool last) {   // S_w = Q_w K^T for ring block gi (the caller has waited for it)
         if (elect_one()) {
-          const uint32_t v_addr = smem_u32(smem + Attn3Smem::kKV + stage * 2 * kAtTile + kAtTile);
+          const int stage = (int)(gi % kAt3Stages);
+          const uint64_t da = make_sw128_desc(q_addr + w * kAtTile);
+          const uint64_t db = make_sw128_desc(smem_u32(smem + Attn3Smem::kKV + stage * 2 * kAtTile));
 #pragma unroll
-          for (int kk = 0; kk < 8; ++kk) {
-            // A = P_w: 16 keys per K step = 8 columns of packed bf16 pairs; B = V: 16 rows of 128 bytes per K step
-            const uint64_t db = make_sw128_mn_desc(v_addr + kk * 2048);
-            umma_bf16_ts(tmem_o + w * 64, tmem_p + w * 64 + kk * 8, db, idesc_o, (j | kk) != 0 ? 1u : 0u);
-          }
-          umma_commit(bar_o_done + w);
-          if (w == 1) umma_commit(bar_kv_empty + stage);   // every MMA that reads K_j / V_j has been issued
+          for (int k = 0; k < 4; ++k) umma_bf16(tmem_s + w * 128, da + 2 * k, db + 2 * k, idesc_s, k != 0 ? 1u : 0u);
+          umma_commit(bar_s_full + w);
+          if (last && w == 1) umma_commit(bar_q_empty + qb);   // the item's last products that read Q
         }
         __syncwarp();
+      };
+      mbar_wait(bar_kv_full + g % kAt3Stages, (g / kAt3Stages) & 1u);
+      tc_fence_after();
+      issue_s(0, g, nkb == 1);
+      issue_s(1, g, nkb == 1);
+      for (int j = 0; j < nkb; ++j, ++g) {
+        const int stage = (int)(g % kAt3Stages);
+        if (j + 1 < nkb) {   // K_j+1 (and V_j+1) landed: both query tiles' next S products need it
+          mbar_wait(bar_kv_full + (g + 1) % kAt3Stages, ((g + 1) / kAt3Stages) & 1u);
+        }
+        for (int w = 0; w < 2; ++w) {
+          mbar_wait(bar_p_full + w, g & 1u);   // P_w,j is in tensor memory, so S_w,j has been read
+          tc_fence_after();
+          if (j + 1 < nkb) issue_s(w, g + 1, j + 2 == nkb);   // ahead of PV_w,j: the softmax warps restart one MMA earlier
+          if (elect_one()) {
+            const uint32_t v_addr = smem_u32(smem + Attn3Smem::kKV + stage * 2 * kAtTile + kAtTile);
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk) {
+              // A = P_w: 16 keys per K step = 8 columns of packed bf16 pairs; B = V: 16 rows of 128 bytes per K step
+              const uint64_t db = make_sw128_mn_desc(v_addr + kk * 2048);
+              umma_bf16_ts(tmem_o + w * 64, tmem_p + w * 64 + kk * 8, db, idesc_o, (j | kk) != 0 ? 1u : 0u);
+            }
+            umma_commit(bar_o_done + w);
+            if (w == 1) umma_commit(bar_kv_empty + stage);   // every MMA that reads K_j / V_j has been issued
+          }
+          __syncwarp();
+        }
       }
     }
   } else {
@@ -292,11 +328,19 @@ attention3_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat
     const uint32_t t_p = tmem_p + lane_sel + w * 64;
     const uint32_t t_o = tmem_o + lane_sel + w * 64;
     constexpr float kTau = 8.0f;                  // the reference exponent moves only past 2^8 (P <= 256: exact in f32 sums)
+    uint32_t g = 0;                               // key blocks processed by this CTA so far (barrier parities)
+    for (int it = 0;; ++it) {
+    const int qb = it & 1;
+    mbar_wait(bar_q_full + qb, (uint32_t)((it >> 1) & 1));
+    const int item = s_item[qb];
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_q_empty + qb);
+    if (item < 0) break;
     float m_ref = -INFINITY, m_seen = -INFINITY, l_run = 0.0f;
     float alpha_pend = 1.0f;                      // O rescale owed from the previous block's reference move
     bool rescale_pend = false;                    // warp-uniform
-    for (int j = 0; j < nkb; ++j) {
-      mbar_wait(bar_s_full + w, (uint32_t)(j & 1));
+    for (int j = 0; j < nkb; ++j, ++g) {
+      mbar_wait(bar_s_full + w, g & 1u);
       tc_fence_after();
       const int valid = S - j * 128;  // keys valid in this block (>= 128 except the last)
       if (j == 0) {
@@ -308,7 +352,7 @@ attention3_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat
       // from the last reference move goes here too
       auto pre = [&]() {
         if (j >= 1) {
-          mbar_wait(bar_o_done + w, (uint32_t)((j - 1) & 1));
+          mbar_wait(bar_o_done + w, (g - 1) & 1u);
           tc_fence_after();
           if (rescale_pend) at3_rescale_o(t_o, alpha_pend);
         }
@@ -354,10 +398,10 @@ attention3_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat
     }
     // ---- O / l -> bf16 ----
     {
-      const int jp = nkb - 1;
-      mbar_wait(bar_o_done + w, (uint32_t)(jp & 1));
+      mbar_wait(bar_o_done + w, (g - 1) & 1u);   // PV of the item's last key block
       tc_fence_after();
-      const int q = q0 + w * 128 + row;
+      const int qp = item % n_qp, bh = item / n_qp, h = bh % H, b = bh / H;   // decoded here: nothing of it is live in the loop
+      const int q = qp * 256 + w * 128 + row;
       const float inv = 1.0f / l_run;
       uint4* dst = reinterpret_cast<uint4*>(out + ((long long)b * S + q) * D + h * 64);
 #pragma unroll
@@ -375,6 +419,7 @@ attention3_sm100_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat
         }
       }
     }
+    }   // items
   }
 
   tc_fence_before();

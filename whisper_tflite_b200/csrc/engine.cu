@@ -631,7 +631,10 @@ int wt_engine::attention_bf16(const void* qkv_, void* out, int n_clips, int S, i
   WT_TRY(get_map(&mq, qkv_, 3, qd, qs, qbox));
   stage = ST_ENC_ATTN;
   pre_launch();
-  wt::attention3_sm100_kernel<<<dim3((S + 255) / 256, H, n_clips), wt::kAt3Threads, wt::Attn3Smem::kTotal, stream>>>(mq, (bf16*)out, S, H);
+  if (!gemm_sched) return fail(WT_ERR_STATE, "tile scheduler counters not allocated (engine not initialised)");
+  const int n_items = n_clips * H * ((S + 255) / 256);
+  wt::attention3_sm100_kernel<<<n_items < num_sms ? n_items : num_sms, wt::kAt3Threads, wt::Attn3Smem::kTotal, stream>>>(
+      mq, (bf16*)out, S, H, n_clips, gemm_sched);
   return check_launch("attention3_sm100_kernel");
 }
 
