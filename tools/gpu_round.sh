@@ -2,7 +2,7 @@
 # One GPU-box visit: parity tests, bench line, ncu launch list, ncu full captures of the top kernels.
 # usage: tools/gpu_round.sh <tag> [kernel-regex ...]
 set -u
-TAG=${1:-r02j}; shift || true
+TAG=${1:-r02k}; shift || true
 OUT=gpurun_out
 mkdir -p $OUT
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $OUT/${TAG}_smi.csv 2>&1
