@@ -236,6 +236,7 @@ struct wt_engine {
   // (measured at N = 8 with 8 engines per GPU: e2e 1.59 M audio-s/s polling, 1.70 M sleeping; one GPU: no difference). A
   // blocking event puts the waiting thread to sleep instead.
   // WT_SPIN_SYNC=1 restores the polling wait (lowest wake-up latency for a single call).
+  bool defer_pcm_wait = false;   // log_mel: do not wait for the host PCM copy (the caller waits at the end of its pass)
   cudaEvent_t sync_ev = nullptr;
   cudaError_t wait_stream() {
     static const char* spin = getenv("WT_SPIN_SYNC");
@@ -752,7 +753,9 @@ int wt_engine::log_mel(const void* pcm, int n_clips, int n_samples, int pcm_mem,
       WT_CUDA_OK(cudaMemcpyAsync(out, d_mel, (size_t)n_clips * n_mel * n_len * 4,
                                  out_mem == WT_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, stream));
   }
-  if (pcm_mem == WT_HOST || (out && out_mem == WT_HOST)) WT_CUDA_OK(wait_stream());
+  // the caller's host buffers are free again when the call returns — unless the caller (wt_transcribe_tokens) ends
+  // with a wait of its own and wants the whole pass enqueued first
+  if ((pcm_mem == WT_HOST && !defer_pcm_wait) || (out && out_mem == WT_HOST)) WT_CUDA_OK(wait_stream());
   return WT_OK;
 }
 
@@ -1483,9 +1486,22 @@ int wt_transcribe_tokens(wt_engine* e, const float* pcm, int n_clips, int n_samp
   if (!e) return fail(WT_ERR_INVALID, "engine is null");
   cudaSetDevice(e->device);
   if (n_samples != WT_N_SAMPLES) return fail(WT_ERR_INVALID, "wt_transcribe_tokens needs 480000-sample windows (pad/trim like whisper.cpp:753)");
-  WT_TRY(e->log_mel(pcm, n_clips, n_samples, pcm_mem == WT_HOST ? WT_HOST : WT_DEVICE, nullptr, WT_DEVICE, false));
-  WT_TRY(e->encode(nullptr, n_clips, WT_DEVICE, nullptr, WT_DEVICE, true));
-  return e->decode(n_clips, prompt, prompt_len, max_total_tokens, eot, ids_out, lens_out, out_mem);
+  // one host wait per pass: mel, encoder and decoder are enqueued back to back, the wait that frees the caller's PCM
+  // buffer is the one that delivers the ids (or, with device-resident outputs, a single wait at the end)
+  e->defer_pcm_wait = true;
+  int st = e->log_mel(pcm, n_clips, n_samples, pcm_mem == WT_HOST ? WT_HOST : WT_DEVICE, nullptr, WT_DEVICE, false);
+  e->defer_pcm_wait = false;
+  if (st != WT_OK) {
+    if (pcm_mem == WT_HOST) e->wait_stream();
+    return st;
+  }
+  st = e->encode(nullptr, n_clips, WT_DEVICE, nullptr, WT_DEVICE, true);
+  if (st == WT_OK) st = e->decode(n_clips, prompt, prompt_len, max_total_tokens, eot, ids_out, lens_out, out_mem);
+  if (pcm_mem == WT_HOST && (st != WT_OK || out_mem != WT_HOST)) {
+    cudaError_t ce = e->wait_stream();
+    if (st == WT_OK && ce != cudaSuccess) st = fail(WT_ERR_CUDA, "stream wait failed: %s", cudaGetErrorString(ce));
+  }
+  return st;
 }
 
 int wt_log_mel_i16(wt_engine* e, const int16_t* pcm, int n_clips, int n_samples, int pcm_mem, float* mel_out, int out_mem) {
@@ -1500,9 +1516,22 @@ int wt_transcribe_tokens_i16(wt_engine* e, const int16_t* pcm, int n_clips, int 
   if (!e) return fail(WT_ERR_INVALID, "engine is null");
   cudaSetDevice(e->device);
   if (n_samples != WT_N_SAMPLES) return fail(WT_ERR_INVALID, "wt_transcribe_tokens_i16 needs 480000-sample windows (pad/trim like whisper.cpp:753)");
-  WT_TRY(e->log_mel(pcm, n_clips, n_samples, pcm_mem == WT_HOST ? WT_HOST : WT_DEVICE, nullptr, WT_DEVICE, false, true));
-  WT_TRY(e->encode(nullptr, n_clips, WT_DEVICE, nullptr, WT_DEVICE, true));
-  return e->decode(n_clips, prompt, prompt_len, max_total_tokens, eot, ids_out, lens_out, out_mem);
+  // one host wait per pass: mel, encoder and decoder are enqueued back to back, the wait that frees the caller's PCM
+  // buffer is the one that delivers the ids (or, with device-resident outputs, a single wait at the end)
+  e->defer_pcm_wait = true;
+  int st = e->log_mel(pcm, n_clips, n_samples, pcm_mem == WT_HOST ? WT_HOST : WT_DEVICE, nullptr, WT_DEVICE, false, true);
+  e->defer_pcm_wait = false;
+  if (st != WT_OK) {
+    if (pcm_mem == WT_HOST) e->wait_stream();
+    return st;
+  }
+  st = e->encode(nullptr, n_clips, WT_DEVICE, nullptr, WT_DEVICE, true);
+  if (st == WT_OK) st = e->decode(n_clips, prompt, prompt_len, max_total_tokens, eot, ids_out, lens_out, out_mem);
+  if (pcm_mem == WT_HOST && (st != WT_OK || out_mem != WT_HOST)) {
+    cudaError_t ce = e->wait_stream();
+    if (st == WT_OK && ce != cudaSuccess) st = fail(WT_ERR_CUDA, "stream wait failed: %s", cudaGetErrorString(ce));
+  }
+  return st;
 }
 
 int wt_get_step_logits(wt_engine* e, int step, int n_clips, float* out, int out_mem) {
