@@ -152,7 +152,7 @@ def test_api_errors():
 
 @pytest.mark.parametrize("size,n_clips", [("micro", 5), ("tiny", 3), ("tiny", 64)])
 def test_persistent_decoder_matches_per_kernel_decoder(size, n_clips):
-    """The one-launch cooperative decoder (decoder_sm100.cuh) against the per-kernel decoder it replaces (kept as
+    """The one-launch streaming decoder (decoder_stream_sm100.cuh) against the per-kernel decoder it replaces (kept as
     WT_DECODER=legacy): same bf16 operands, so logits agree to accumulation-order noise and ids wherever the margin allows."""
     from whisper_tflite_b200 import capi
     path, dims, W = weight_file(size)

@@ -1,5 +1,5 @@
 """Encoder attention kernel alone on the bench shape (64 clips x 6 heads x 1500 keys, head_dim 64), CUDA events,
-inputs of 2 x 221 MB rotating (> L2).   usage: [WT_ATTN=2] python tools/attn_bench.py [B] [H] [iters]"""
+inputs of 2 x 221 MB rotating (> L2).   usage: python tools/attn_bench.py [B] [H] [iters]"""
 import os
 import sys
 
@@ -32,5 +32,5 @@ flop = 4.0 * B * H * S * S * 64
 ref = torch.softmax((qkvs[(iters - 1) % 2][:2, :, :64].float() @ qkvs[(iters - 1) % 2][:2, :, H * 64:H * 64 + 64].float().transpose(1, 2)) * 0.125, -1) \
     @ qkvs[(iters - 1) % 2][:2, :, 2 * H * 64:2 * H * 64 + 64].float()
 err = (out[:2, :, :64].float() - ref).abs().max().item() / ref.abs().max().item()
-print(f"attention kernel={os.environ.get('WT_ATTN', '3')} B={B} H={H}: {ms:.4f} ms per launch, {flop / ms / 1e9:.1f} TFLOP/s, "
+print(f"attention3_sm100_kernel B={B} H={H}: {ms:.4f} ms per launch, {flop / ms / 1e9:.1f} TFLOP/s, "
       f"rel-to-max err (head 0, 2 clips) {err:.2e}")

@@ -1,6 +1,6 @@
 """Per-stage device times of one engine on the bench workload (whisper-tiny, 64 clips), engine-side CUDA events.
 
-    python tools/stage_time.py [n_clips] [model]        env switches (WT_ATTN, WT_DECODER ...) apply as usual
+    python tools/stage_time.py [n_clips] [model]        env switches (WT_GEMM_LEAN, WT_DECODER ...) apply as usual
 """
 import os
 import sys

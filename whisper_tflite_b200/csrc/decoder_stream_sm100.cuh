@@ -4,7 +4,7 @@
 // the cross-attention K/V stream, its slice of the tied logits matrix — through a single shared-memory ring of
 // cp.async.bulk (TMA) copies, in program order, as far ahead as the ring allows.
 //
-// What the ncu source page of the first design (decoder_sm100.cuh) showed: no hot spot, 3.1 G warp instructions,
+// What the ncu source page of the first design (round 1's decoder_sm100.cuh, since removed) showed: no hot spot, 3.1 G warp instructions,
 // ~2200 per warp and projection phase, almost all of it address arithmetic, predicates and staging around 24 MMAs,
 // executed by 2 warps per scheduler with nothing to hide fixed latencies behind (stall_wait 23 %, barrier 21 %,
 // long scoreboard 20 %). The phases were instruction- and latency-bound, 10-17 us each. Here:
@@ -242,7 +242,7 @@ __device__ __forceinline__ void ds_cluster_sync(uint8_t* smem, const DsParams& p
 // ---------------------------------------------------------------------------------------------------
 // Weight packing (engine creation). A "unit" is the 512 bytes one warp feeds to two m16n8k16 MMAs: for 8-column
 // group g and 32-wide k block kb, lane (gq = lane / 4, t = lane % 4) holds W[g*8 + gq][kb*32 + t*8 .. +8) — the K
-// permutation inside a k block is the one the activation fragments use (dec_mma_w in decoder_sm100.cuh). Units are
+// permutation inside a k block is the one the activation fragments use (mma_bf16_16816 in dec_common.cuh). Units are
 // ordered the way the stream delivers them: CTA slice (gpc groups) -> round of 8 groups (one per consumer warp) ->
 // k phase (upw k blocks) -> warp -> unit, so a ring stage is one contiguous copy and warp w's share of it sits at
 // w * upw * 512.

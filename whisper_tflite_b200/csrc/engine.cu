@@ -870,7 +870,7 @@ int wt_engine::load_model(const char* path) {
     WT_TRY(up_plain(L.fc1, p + ".mlp.0", 4 * d, d, true));
     WT_TRY(up_plain(L.fc2, p + ".mlp.2", d, 4 * d, true));
     if (want_persistent) {
-      // streaming layout of the persistent decoder: [clip][head][chunk][K rows | V rows] (decoder_sm100.cuh)
+      // streaming layout of the persistent decoder: [clip][head][chunk][K rows | V rows] (decoder_stream_sm100.cuh)
       const size_t cpp = (size_t)(S + wt::kXaChunk - 1) / wt::kXaChunk;
       WT_TRY(alloc_bytes(&L.kvx, B * (size_t)H * cpp * 2 * wt::kXaChunk * 64 * esz, true));
     } else {
