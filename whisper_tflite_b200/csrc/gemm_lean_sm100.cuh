@@ -12,6 +12,11 @@
 
 #include "gemm_sm100.cuh"
 
+#ifndef LEAN_PROBE
+#define LEAN_PROBE 0   // timing probes (build.build_cuda_variant + WT_LIB): 1 = no epilogue work, 2 = no operand loads, 4 = no C
+                       // stores (bits combine); results are garbage
+#endif
+
 namespace wt {
 
 constexpr int kLeanEpiWarps = 16;
@@ -172,7 +177,9 @@ __device__ __forceinline__ void gemm_lean_epilogue(const GemmBf16Params& p, cons
     __syncwarp();
     const int bp = b == 0 ? kBoxes - 1 : b - 1;   // the box of chunk c - 1 (== the box of chunk c + kBoxes - 1)
     if (lane == 0) {
+#if !(LEAN_PROBE & 4)
       tma_store_3d(map_c, scr + b * 2048, ncol0 + c * 32, rowq, batch);
+#endif
       bulk_commit();
       if (tma_add && c + kBoxes - 1 < kChunks) {   // kBoxes >= 2 with an addend
         asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // every store but chunk c's has read its box
@@ -267,10 +274,15 @@ gemm_lean_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
           mbar_wait(bar_empty + stage, phase ^ 1);
           uint8_t* sa = s_stage + stage * S::kStageBytes;
           uint8_t* sb = sa + S::kABytes;
+#if LEAN_PROBE & 2
+          (void)sa; (void)sb; (void)tn; (void)batch; (void)row0;
+          mbar_arrive(bar_full + stage);
+#else
           mbar_expect_tx(bar_full + stage, S::kStageBytes);
           const int tap = kb / p.kblocks_per_tap, kc = kb - tap * p.kblocks_per_tap;
           tma_load_3d(sa, &map_a, bar_full + stage, p.tap_c0[tap] + kc * kGemmBK, row0 + p.tap_row[tap], batch);
           tma_load_2d(sb, &map_w, bar_full + stage, tap * p.tap_k + kc * kGemmBK, tn * BN);
+#endif
           if (++stage == n_stages) { stage = 0; phase ^= 1; }
         }
       }
@@ -351,11 +363,15 @@ gemm_lean_sm100_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
       mbar_wait(bar_tfull + acc, acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(lane_q * 32) << 16) + acc * BN + half * kHalf;
+#if LEAN_PROBE & 1
+      (void)t_row; (void)rot; (void)add_ph;
+#else
       if (has_kv) {
         if constexpr (kChunks % 2 == 0) gemm_lean_epilogue_kv<kChunks>(p, &map_c, t_row, scr, lane, lane_q, batch, row0, ncol0);
       } else {
         gemm_lean_epilogue<kChunks>(p, &map_c, &map_add, bar_add, add_ph, rot, t_row, n_boxes, scr, lane, rowq, batch, ncol0);
       }
+#endif
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + acc);
