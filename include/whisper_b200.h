@@ -83,7 +83,8 @@ WT_API int wt_engine_dims(const wt_engine* e, wt_dims* out);
 WT_API int wt_set_mel_filters(wt_engine* e, const float* filters, int n_mel, int n_freq);
 
 /* Work is enqueued on `cuda_stream` (a cudaStream_t; NULL = the engine's own stream). Calls taking only
- * WT_DEVICE buffers return after enqueueing; calls touching a WT_HOST buffer synchronise before returning. */
+ * WT_DEVICE buffers return after enqueueing; calls touching a WT_HOST buffer synchronise before returning. Changing the
+ * stream waits for the work still in flight on the previous one (an engine's buffers belong to one stream at a time). */
 WT_API int wt_set_stream(wt_engine* e, void* cuda_stream);
 
 /* Clips per thread-block cluster of the persistent greedy decoder (1..16; 0 = automatic: spread the batch over every

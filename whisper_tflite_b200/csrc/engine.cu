@@ -1450,7 +1450,14 @@ int wt_set_mel_filters(wt_engine* e, const float* filters, int n_mel, int n_freq
 
 int wt_set_stream(wt_engine* e, void* s) {
   if (!e) return fail(WT_ERR_INVALID, "engine is null");
-  e->stream = s ? (cudaStream_t)s : e->own_stream;
+  cudaStream_t ns = s ? (cudaStream_t)s : e->own_stream;
+  if (ns != e->stream) {
+    // the engine's buffers and its tile-scheduler counters belong to ONE stream at a time: work still in flight on the
+    // old stream finishes before anything is enqueued on the new one
+    cudaSetDevice(e->device);
+    WT_CUDA_OK(e->wait_stream());
+    e->stream = ns;
+  }
   return WT_OK;
 }
 
