@@ -43,3 +43,15 @@ def test_product_does_not_import_oracle():
                 src = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
                 assert "oracle/" not in src or f == "synth.py", f
+
+
+def test_header_is_plain_c():
+    """include/whisper_b200.h is the drop-in boundary: it must compile as C99 (no C++ or torch types in the signatures)."""
+    import shutil
+    import subprocess
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if not cc:
+        pytest.skip("no C compiler")
+    hdr = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "whisper_b200.h")
+    r = subprocess.run([cc, "-fsyntax-only", "-x", "c", "-std=c99", "-Wall", "-Wextra", "-Werror", hdr], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
